@@ -1,0 +1,137 @@
+/* include/srt_backend.h -- C ABI of the B200 (sm_100a) path-tracing backend.
+ *
+ * This is the drop-in boundary for ONE hot path of Ne0nWinds/SIMD-Ray-Tracer: the per-tile
+ * callbacks RenderTile / RenderTileScalar (main.cpp:348-640) that the platform work queue
+ * runs when the application calls WorkQueueStart (main.cpp:852, base.h:174).  A maintainer
+ * of the reference replaces that kick with srt_render(); WorkQueueHasCompleted /
+ * WorkQueueWaitUntilCompletion / WorkQueueGetCompletionTime (base.h:175-178) map to
+ * srt_poll / srt_wait.  INTEGRATION.md shows the exact binding.
+ *
+ * Plain C, plain pointers and sizes; no C++ or torch types.  Every function returns
+ * SRT_OK (0) or a negative srt_status; srt_last_error() describes the last failure.
+ * The library has NO CPU fallback: without a CUDA device srt_create fails.
+ * One host thread per handle; at most one render in flight per handle.
+ */
+#ifndef SRT_BACKEND_H
+#define SRT_BACKEND_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    SRT_OK = 0,
+    SRT_ERR_INVALID = -1,     /* bad argument / call order */
+    SRT_ERR_CUDA = -2,        /* CUDA runtime error (see srt_last_error) */
+    SRT_ERR_NO_DEVICE = -3,   /* no usable sm_100 device */
+    SRT_ERR_TOO_LARGE = -4    /* scene / image exceeds a backend limit */
+} srt_status;
+
+/* POD mirror of `material`, main.cpp:11-16 (v3 is 16 bytes: x,y,z,_w; base.h:357-375). 48 B */
+typedef struct srt_material {
+    float color[4];
+    float emissive[4];
+    float specular;
+    float index_of_refraction;
+    float _pad[2];
+} srt_material;
+
+/* POD mirror of `scalar_sphere`, main.cpp:17-21. 80 B: Scene.ScalarSpheres.Data can be
+ * passed as is. */
+typedef struct srt_sphere {
+    float position[4];
+    float radius;
+    float _pad[3];
+    srt_material material;
+} srt_sphere;
+
+/* POD mirror of the geometric part of `camera_info`, main.cpp:270-277. */
+typedef struct srt_camera {
+    float camera_position[4];
+    float camera_z[4];
+    float camera_x[4];
+    float camera_y[4];
+    float film_center[4];
+    float film_w;
+    float film_h;
+    float _pad[2];
+} srt_camera;
+
+/* Which tile callback's semantics to reproduce (render_params.EnableSIMD, base.h:157-161,
+ * selected at main.cpp:852-856), and which arithmetic profile of x64_math.h. */
+typedef struct srt_scene_options {
+    int32_t use_sky_color;  /* scene.UseSkyColor, main.cpp:44 */
+    int32_t lane_width;     /* 8 or 4: RenderTile with SIMD_WIDTH lanes (tie-break + sticky
+                               inside flag of main.cpp:419-427); 1: RenderTileScalar */
+    int32_t fma_dot;        /* 1: v3x8::Dot/LengthSquared use FMA (x64_math.h:409-420);
+                               0: mul,mul,mul,add,add (x64_math.h:299-309) */
+    int32_t _reserved;
+} srt_scene_options;
+
+typedef enum {
+    SRT_ACCUM_MEAN = 0,  /* exact running mean of main.cpp:484-489 (single device) */
+    SRT_ACCUM_SUM = 1    /* plain f32 sum of the samples' radiance; combine across devices,
+                            then srt_resolve_sum() */
+} srt_accum_mode;
+
+typedef struct srt_render_args {
+    uint32_t first_sample;   /* absolute index k of the first sample (PreviousRayCount, main.cpp:7) */
+    uint32_t n_samples;      /* samples per pixel rendered by this call */
+    uint32_t sample_stride;  /* k advances by this; 1 = contiguous; G for sample sharding over G devices */
+    uint32_t accum_mode;     /* srt_accum_mode */
+    uint64_t stream_base;    /* per-path RNG stream = scramble(stream_base + k*W*H + y*W + x),
+                                scramble = main.cpp:667-676 on a 64-bit index */
+    uint32_t record_primary; /* 1: record primary-ray hit/primitive/t of sample `first_sample` */
+    uint32_t _reserved;
+} srt_render_args;
+
+typedef struct srt_backend srt_backend;
+
+/* Lifetime. device_id: CUDA ordinal. */
+int srt_create(srt_backend **out, int device_id);
+void srt_destroy(srt_backend *b);
+const char *srt_last_error(const srt_backend *b);   /* b may be NULL: last create error */
+
+/* Scene upload (replaces ConvertScalarSpheresToSIMDSpheres' SoA, main.cpp:73-91): copies;
+ * the caller keeps ownership of `spheres`. */
+int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
+                  const srt_scene_options *options);
+
+/* (Re)allocate PreviousImage (f32x4) + CurrentImage (RGBA8) on the device and reset the
+ * accumulation, like main.cpp:797-804. */
+int srt_resize(srt_backend *b, uint32_t width, uint32_t height);
+/* Reset only (camera moved / key R, main.cpp:791-798): zeroes the accumulator. */
+int srt_reset_accumulation(srt_backend *b);
+/* Optional: render into caller-owned DEVICE buffers (accum: W*H*4 f32, rgba: W*H u32),
+ * e.g. to run a collective on them. NULL restores the internal buffers. */
+int srt_bind_device_buffers(srt_backend *b, void *accum_dev, void *rgba_dev);
+
+/* Kick one batch: the WorkQueueStart replacement. Asynchronous. */
+int srt_render(srt_backend *b, const srt_camera *camera, const srt_render_args *args);
+/* 1 = finished, 0 = still running (WorkQueueHasCompleted). */
+int srt_poll(srt_backend *b);
+/* Block until finished (WorkQueueWaitUntilCompletion); out_ms = device time of the last
+ * batch (CUDA events), out_rays = path segments cast by it, counted like main.cpp:390. */
+int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays);
+
+/* accum holds a SUM over `total_samples`: mean = sum * (1/N), tonemap + pack into rgba
+ * (main.cpp:312-346). Asynchronous on the backend stream; ordered after prior renders. */
+int srt_resolve_sum(srt_backend *b, uint32_t total_samples);
+
+/* Read-backs into HOST buffers (row 0 = image bottom, as in the reference). */
+int srt_read_rgba8(srt_backend *b, void *dst /* W*H*4 bytes */);
+int srt_read_accum(srt_backend *b, float *dst /* W*H*4 floats */);
+int srt_read_primary(srt_backend *b, uint32_t *prim /* 0xFFFFFFFF = miss */, float *t /* 1e30 = miss */);
+
+/* Device pointers / stream of the current buffers (for collectives and graphs). */
+void *srt_accum_device_ptr(srt_backend *b);
+void *srt_rgba_device_ptr(srt_backend *b);
+void *srt_cuda_stream(srt_backend *b);
+
+/* Introspection for benchmarks: SM count, clock (kHz), kernel launches issued so far. */
+int srt_device_info(srt_backend *b, int *sm_count, int *clock_khz, uint64_t *launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SRT_BACKEND_H */

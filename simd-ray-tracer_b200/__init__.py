@@ -1,0 +1,183 @@
+"""simd-ray-tracer_b200: B200-native backend for SIMD-Ray-Tracer's path-tracing hot path.
+
+The product is the C-ABI shared library libsrt_cuda.so (include/srt_backend.h) plus the
+C++ host mirror of the reference's OnInit/OnRender (host/).  This Python module is only a
+thin ctypes binding for tests and bench.py; it never computes pixels itself and raises if
+the CUDA library is missing (there is no CPU fallback).
+
+Import with importlib (the directory name has a hyphen):
+    srt = importlib.import_module("simd-ray-tracer_b200")
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+PKG_DIR = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = _build.LIB
+
+# ---- POD mirrors of include/srt_backend.h -------------------------------------------------
+sphere_dtype = np.dtype([
+    ("position", np.float32, 4), ("radius", np.float32), ("_pad", np.float32, 3),
+    ("color", np.float32, 4), ("emissive", np.float32, 4),
+    ("specular", np.float32), ("ior", np.float32), ("_pad2", np.float32, 2)])
+camera_dtype = np.dtype([
+    ("position", np.float32, 4), ("z", np.float32, 4), ("x", np.float32, 4), ("y", np.float32, 4),
+    ("film_center", np.float32, 4), ("film_w", np.float32), ("film_h", np.float32), ("_pad", np.float32, 2)])
+assert sphere_dtype.itemsize == 80 and camera_dtype.itemsize == 96
+
+ACCUM_MEAN, ACCUM_SUM = 0, 1
+
+EXPORTS = [
+    "srt_create", "srt_destroy", "srt_last_error", "srt_set_scene", "srt_resize",
+    "srt_reset_accumulation", "srt_bind_device_buffers", "srt_render", "srt_poll", "srt_wait",
+    "srt_resolve_sum", "srt_read_rgba8", "srt_read_accum", "srt_read_primary",
+    "srt_accum_device_ptr", "srt_rgba_device_ptr", "srt_cuda_stream", "srt_device_info",
+]
+
+
+class SceneOptions(C.Structure):
+    _fields_ = [("use_sky_color", C.c_int32), ("lane_width", C.c_int32), ("fma_dot", C.c_int32), ("_reserved", C.c_int32)]
+
+
+class RenderArgs(C.Structure):
+    _fields_ = [("first_sample", C.c_uint32), ("n_samples", C.c_uint32), ("sample_stride", C.c_uint32),
+                ("accum_mode", C.c_uint32), ("stream_base", C.c_uint64), ("record_primary", C.c_uint32),
+                ("_reserved", C.c_uint32)]
+
+
+class SrtError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen libsrt_cuda.so (no compute). Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise SrtError(f"{LIB_PATH} is missing: run __graft_entry__.build() (nvcc). There is no CPU fallback.")
+    L = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    L.srt_create.argtypes = [C.POINTER(vp), C.c_int]
+    L.srt_destroy.argtypes = [vp]
+    L.srt_destroy.restype = None
+    L.srt_last_error.argtypes = [vp]
+    L.srt_last_error.restype = C.c_char_p
+    L.srt_set_scene.argtypes = [vp, vp, C.c_uint32, C.POINTER(SceneOptions)]
+    L.srt_resize.argtypes = [vp, C.c_uint32, C.c_uint32]
+    L.srt_reset_accumulation.argtypes = [vp]
+    L.srt_bind_device_buffers.argtypes = [vp, vp, vp]
+    L.srt_render.argtypes = [vp, vp, C.POINTER(RenderArgs)]
+    L.srt_poll.argtypes = [vp]
+    L.srt_wait.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
+    L.srt_resolve_sum.argtypes = [vp, C.c_uint32]
+    L.srt_read_rgba8.argtypes = [vp, vp]
+    L.srt_read_accum.argtypes = [vp, vp]
+    L.srt_read_primary.argtypes = [vp, vp, vp]
+    for f in ("srt_accum_device_ptr", "srt_rgba_device_ptr", "srt_cuda_stream"):
+        getattr(L, f).argtypes = [vp]
+        getattr(L, f).restype = vp
+    L.srt_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
+    _lib = L
+    return L
+
+
+class Backend:
+    """One handle of the C ABI. Mirrors the call order a reference maintainer would use."""
+
+    def __init__(self, device=0):
+        self.L = load_library()
+        self.h = C.c_void_p()
+        rc = self.L.srt_create(C.byref(self.h), device)
+        if rc != 0:
+            raise SrtError(f"srt_create failed ({rc}): {self.L.srt_last_error(None).decode()}")
+        self.width = self.height = 0
+
+    def _check(self, rc):
+        if rc < 0:
+            raise SrtError(f"srt error {rc}: {self.L.srt_last_error(self.h).decode()}")
+        return rc
+
+    def close(self):
+        if self.h:
+            self.L.srt_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_scene(self, spheres, use_sky, lane_width=8, fma_dot=True):
+        spheres = np.ascontiguousarray(spheres)
+        assert spheres.dtype.itemsize == 80
+        opt = SceneOptions(int(use_sky), lane_width, int(fma_dot), 0)
+        self._check(self.L.srt_set_scene(self.h, spheres.ctypes.data, len(spheres), C.byref(opt)))
+
+    def resize(self, w, h):
+        self._check(self.L.srt_resize(self.h, w, h))
+        self.width, self.height = w, h
+
+    def reset(self):
+        self._check(self.L.srt_reset_accumulation(self.h))
+
+    def bind_device_buffers(self, accum_ptr, rgba_ptr):
+        self._check(self.L.srt_bind_device_buffers(self.h, accum_ptr, rgba_ptr))
+
+    def render(self, camera, first_sample=0, n_samples=1, stride=1, mode=ACCUM_MEAN, stream_base=0, record_primary=False):
+        cam = np.ascontiguousarray(camera)
+        args = RenderArgs(first_sample, n_samples, stride, mode, stream_base, int(record_primary), 0)
+        self._check(self.L.srt_render(self.h, cam.ctypes.data, C.byref(args)))
+
+    def poll(self):
+        return self._check(self.L.srt_poll(self.h)) == 1
+
+    def wait(self):
+        ms, rays = C.c_double(), C.c_uint64()
+        self._check(self.L.srt_wait(self.h, C.byref(ms), C.byref(rays)))
+        return ms.value, rays.value
+
+    def resolve_sum(self, total_samples):
+        self._check(self.L.srt_resolve_sum(self.h, total_samples))
+
+    def read_rgba8(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width), np.uint32)
+        self._check(self.L.srt_read_rgba8(self.h, out.ctypes.data))
+        return out
+
+    def read_accum(self, out=None):
+        if out is None:
+            out = np.empty((self.height, self.width, 4), np.float32)
+        self._check(self.L.srt_read_accum(self.h, out.ctypes.data))
+        return out
+
+    def read_primary(self):
+        prim = np.empty((self.height, self.width), np.uint32)
+        t = np.empty((self.height, self.width), np.float32)
+        self._check(self.L.srt_read_primary(self.h, prim.ctypes.data, t.ctypes.data))
+        return prim, t
+
+    def device_info(self):
+        sm, khz, n = C.c_int(), C.c_int(), C.c_uint64()
+        self._check(self.L.srt_device_info(self.h, C.byref(sm), C.byref(khz), C.byref(n)))
+        return dict(sm_count=sm.value, clock_khz=khz.value, launches=n.value)
+
+    @property
+    def accum_ptr(self):
+        return self.L.srt_accum_device_ptr(self.h)
+
+    @property
+    def rgba_ptr(self):
+        return self.L.srt_rgba_device_ptr(self.h)
+
+    @property
+    def stream_ptr(self):
+        return self.L.srt_cuda_stream(self.h)

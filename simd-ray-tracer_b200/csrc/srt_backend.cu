@@ -1,0 +1,555 @@
+// srt_backend.cu -- CUDA kernels (sm_100a) and the C ABI of include/srt_backend.h.
+//
+// Replaces the reference's per-tile callbacks RenderTile / RenderTileScalar
+// (main.cpp:348-640) and the work-queue kick that runs them (main.cpp:852).
+// No CPU fallback: every entry point fails with SRT_ERR_NO_DEVICE / SRT_ERR_CUDA
+// when there is no usable device.
+#include "../../include/srt_backend.h"
+#include "srt_device.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace srt {
+
+constexpr int kBlockThreads = 256;
+constexpr uint32_t kInvalidPixel = 0xFFFFFFFFu;
+
+// Work item i -> pixel: 8x4 pixel blocks, row-major over blocks, so that a fresh warp
+// covers a compact screen patch (coherent primary rays: the rare hit branch and the
+// material branch diverge less).  Returns false for items outside the image.
+__device__ __forceinline__ bool item_to_pixel(const KernelParams &P, uint32_t item, uint32_t &px, uint32_t &py) {
+    const uint32_t blk = item >> 5, in = item & 31u;
+    const uint32_t bx = blk % P.blocks_x, by = blk / P.blocks_x;
+    px = bx * 8u + (in & 7u);
+    py = by * 4u + (in >> 3);
+    return px < P.width && py < P.height;
+}
+
+// ------------------------------------------------------------------------------------------
+// render_paths: the whole per-pixel pipeline A1..A9.
+//
+// Persistent CTAs, one path per thread, PATH REGENERATION: a thread whose path ended
+// (miss or 5th bounce) immediately starts the next sample of its pixel, or pulls the next
+// pixel from a global counter (warp-aggregated atomic), so all 32 lanes of a warp enter
+// the brute-force intersection loop together no matter how many bounces each path takes.
+// A thread owns a pixel for all n_samples of the launch: the running mean lives in
+// registers and the framebuffers are touched once per pixel per launch (16 B read when
+// first_sample > 0, 16 B + 4 B written).  The scene SoA sits in shared memory and is read
+// with warp-uniform LDS.128 broadcasts.
+// ------------------------------------------------------------------------------------------
+template <int W, bool FMA>
+__global__ void __launch_bounds__(kBlockThreads)
+render_paths(const __grid_constant__ KernelParams P) {
+    extern __shared__ float4 s_spheres[];
+    for (uint32_t i = threadIdx.x; i < P.n_pad; i += blockDim.x) s_spheres[i] = P.spheres[i];
+    __syncthreads();
+
+    const unsigned lane = threadIdx.x & 31u;
+    const uint64_t plane = (uint64_t)P.width * P.height;
+    const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
+
+    uint32_t pix = kInvalidPixel, px = 0, py = 0;
+    uint32_t k = k_end;            // current sample index; k == k_end: pixel finished
+    bool active = false, done = false;
+    uint32_t bounce = 0;
+    uint64_t rng = 0;
+    unsigned long long rays = 0;
+    f3 o = mk3(0, 0, 0), d = mk3(0, 0, 0), atten = mk3(1, 1, 1), out = mk3(0, 0, 0);
+    f3 mean = mk3(0, 0, 0);
+
+    for (;;) {
+        // ---- regenerate: finish pixels, fetch new ones, start new paths -------------------
+        bool need = !active && !done && (k == k_end);
+        if (need && pix != kInvalidPixel) {
+            // A8 result + A9 tonemap/pack, main.cpp:484-492
+            P.accum[pix] = make_float4(mean.x, mean.y, mean.z, 1.0f);
+            if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mean.x, mean.y, mean.z);
+            pix = kInvalidPixel;
+        }
+        unsigned m = __ballot_sync(0xFFFFFFFFu, need);
+        while (m) {
+            const unsigned leader = __ffs(m) - 1;
+            unsigned base = 0;
+            if (lane == leader) base = atomicAdd(P.work_counter, __popc(m));
+            base = __shfl_sync(0xFFFFFFFFu, base, leader);
+            if (need) {
+                const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
+                if (item >= P.total_items) { done = true; need = false; }
+                else if (item_to_pixel(P, item, px, py)) {
+                    pix = py * P.width + px;
+                    k = P.first_sample;
+                    need = false;
+                    if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) {
+                        const float4 prev = P.accum[pix];
+                        mean = mk3(prev.x, prev.y, prev.z);
+                    } else {
+                        mean = mk3(0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1) with a zeroed arena
+                    }
+                }
+            }
+            m = __ballot_sync(0xFFFFFFFFu, need);
+        }
+        if (!active && !done) {
+            // A1 primary ray, main.cpp:375-385; stream contract: SURVEY 8c P10
+            rng = stream_seed(P.stream_base + (uint64_t)k * plane + pix);
+            atten = mk3(1.0f, 1.0f, 1.0f);
+            out = mk3(0.0f, 0.0f, 0.0f);
+            const float jx = rand_float(rng, kInvU32Range1, -0.5f);
+            const float jy = rand_float(rng, kInvU32Range1, -0.5f);
+            const float film_x = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)px, jx), 2.0f), (float)P.width));
+            const float film_y = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)py, jy), 2.0f), (float)P.height));
+            const float ax = __fmul_rn(__fmul_rn(film_x, P.cam.film_w), 0.5f);
+            const float ay = __fmul_rn(__fmul_rn(film_y, P.cam.film_h), 0.5f);
+            const f3 cam_x = mk3(P.cam.x[0], P.cam.x[1], P.cam.x[2]);
+            const f3 cam_y = mk3(P.cam.y[0], P.cam.y[1], P.cam.y[2]);
+            const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
+            const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
+            o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+            d = normalize3(sub3(film_p, o));
+            bounce = 0;
+            active = true;
+        }
+        if (__all_sync(0xFFFFFFFFu, done)) break;
+
+        if (active) {
+            // ---- A3/A4 brute-force intersection over ALL spheres, main.cpp:399-455 --------
+            rays += 1;                                                    // main.cpp:390
+            Hit h;
+            if (W == 1) h = intersect_scalar(s_spheres, P.n_pad, P.n_spheres, o, d);
+            else h = intersect_lanes<(W == 1 ? 4 : W), FMA>(s_spheres, P.n_pad, o, d);
+            if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
+                P.tap_t[pix] = h.t;
+                P.tap_prim[pix] = h.prim;
+            }
+            bool path_end = false;
+            if (!h.hit) {
+                if (P.use_sky) {                                          // A5 main.cpp:433-440
+                    const float a = __fmul_rn(__fadd_rn(d.y, 1.0f), 0.5f);
+                    const float ia = __fsub_rn(1.0f, a);
+                    const f3 sky = add3(scale3(ia, mk3(1.0f, 1.0f, 1.0f)), scale3(a, mk3(0.5f, 0.7f, 1.0f)));
+                    out = add3(out, mul3(sky, atten));
+                }
+                path_end = true;
+            } else {
+                // ---- A6 shade + scatter, main.cpp:443-481 ---------------------------------
+                const DevMaterial *M = &P.materials[h.prim];
+                const float4 cs = __ldg(&M->color_spec);
+                const float4 ei = __ldg(&M->emis_ior);
+                const float4 dv = __ldg(&M->derived);
+                out = add3(out, mul3(mk3(ei.x, ei.y, ei.z), atten));
+                atten = mul3(atten, mk3(cs.x, cs.y, cs.z));
+                // winner's HitNormal / NextRayOrigin, recomputed with the ops of main.cpp:423-429
+                const float4 s = s_spheres[h.prim];
+                const f3 sc = sub3(mk3(s.x, s.y, s.z), o);
+                const f3 ip = scale3(h.t, d);
+                o = add3(o, ip);
+                f3 n = normalize3(sub3(ip, sc));
+                const f3 pure = sub3(d, scale3(__fmul_rn(2.0f, dot3(d, n)), n));   // :453
+                if (h.inside) n = neg3(n);
+                if (ei.w == 0.0f) {
+                    const float rx = rand_float(rng, kInvU32Range2, -1.0f);
+                    const float ry = rand_float(rng, kInvU32Range2, -1.0f);
+                    const float rz = rand_float(rng, kInvU32Range2, -1.0f);
+                    const f3 r = normalize3(mk3(rx, ry, rz));                      // :461
+                    const f3 rb = add3(n, r);
+                    d = normalize3(add3(scale3(dv.x, rb), scale3(cs.w, pure)));    // :463-464
+                } else {
+                    const float eta = h.inside ? ei.w : dv.y;                      // :466
+                    const float cd = dot3(neg3(d), n);
+                    const float c = (cd < 1.0f) ? cd : 1.0f;                       // _mm_min_ss :468
+                    const float cc = __fmul_rn(c, c);
+                    const float sn = __fsqrt_rn(__double2float_rn(__dsub_rn(1.0, (double)cc)));   // :469
+                    const bool cant = __fmul_rn(eta, sn) > 1.0f;                   // :471
+                    const f3 perp = scale3(eta, add3(d, scale3(c, n)));            // :472
+                    const float kk = -__fsqrt_rn(fabsf(__fsub_rn(1.0f, dot3(perp, perp))));   // :473
+                    const f3 refr = normalize3(add3(perp, scale3(kk, n)));         // :474
+                    bool reflect = cant;                                            // :476 (|| short-circuit)
+                    if (!cant) reflect = reflectance(c, eta) > rand_float(rng, kInvU32Range1, 0.0f);
+                    d = (reflect && !h.inside) ? pure : refr;
+                }
+                bounce += 1;
+                path_end = (bounce == kMaxBounce);
+            }
+            if (path_end) {
+                if (P.accum_mode == SRT_ACCUM_MEAN) {
+                    // A8 running mean, main.cpp:484-489 (k == PreviousRayCount)
+                    const float total = (float)(k + 1u);
+                    const float wa = __fdiv_rn(1.0f, total);
+                    const float wb = __fdiv_rn((float)k, total);
+                    mean = add3(scale3(wa, out), scale3(wb, mean));
+                } else {
+                    mean = add3(mean, out);
+                }
+                k += P.sample_stride;
+                active = false;
+            }
+        }
+    }
+
+    // rays: one atomic per warp
+    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
+    if (lane == 0 && rays) atomicAdd(P.rays, rays);
+}
+
+// mean = sum * (1/N); tonemap + pack.  HBM-bound: 16 B read + 16 B + 4 B written per pixel.
+__global__ void resolve_sum_kernel(float4 *accum, uint32_t *rgba, uint32_t n_pixels, float inv_n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pixels) return;
+    const float4 s = accum[i];
+    const float r = __fmul_rn(s.x, inv_n), g = __fmul_rn(s.y, inv_n), b = __fmul_rn(s.z, inv_n);
+    accum[i] = make_float4(r, g, b, 1.0f);
+    rgba[i] = pack_rgba8(r, g, b);
+}
+
+} // namespace srt
+
+// =============================================================================================
+// Host side: the C ABI
+// =============================================================================================
+using namespace srt;
+
+struct srt_backend {
+    int device = -1;
+    int sm_count = 0, clock_khz = 0;
+    size_t max_smem_optin = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    // scene
+    float4 *d_spheres = nullptr;
+    DevMaterial *d_materials = nullptr;
+    uint32_t n_spheres = 0, n_pad = 0;
+    srt_scene_options opt = {0, 8, 1, 0};
+    // images
+    uint32_t width = 0, height = 0;
+    float4 *d_accum_own = nullptr, *d_accum = nullptr;
+    uint32_t *d_rgba_own = nullptr, *d_rgba = nullptr;
+    uint32_t *d_tap_prim = nullptr;
+    float *d_tap_t = nullptr;
+    bool tap_valid = false;
+    // counters: [0..7] rays (u64), [8..11] work counter
+    unsigned char *d_counters = nullptr;
+    unsigned long long *h_rays = nullptr;   // pinned
+    bool in_flight = false;
+    uint64_t launches = 0;
+    std::string err;
+};
+
+static std::string g_create_error;
+
+static int fail(srt_backend *b, int code, const std::string &msg) {
+    if (b) b->err = msg; else g_create_error = msg;
+    return code;
+}
+#define SRT_CUDA(b, call)                                                                       \
+    do {                                                                                        \
+        cudaError_t e_ = (call);                                                                \
+        if (e_ != cudaSuccess)                                                                  \
+            return fail((b), SRT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+typedef void (*render_kernel_t)(const KernelParams);
+static render_kernel_t pick_kernel(const srt_scene_options &o) {
+    if (o.lane_width == 1) return render_paths<1, false>;
+    if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true> : render_paths<4, false>;
+    return o.fma_dot ? render_paths<8, true> : render_paths<8, false>;
+}
+
+extern "C" {
+
+const char *srt_last_error(const srt_backend *b) { return b ? b->err.c_str() : g_create_error.c_str(); }
+
+int srt_create(srt_backend **out, int device_id) {
+    if (!out) return fail(nullptr, SRT_ERR_INVALID, "srt_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, SRT_ERR_NO_DEVICE,
+                    std::string("srt_create: no CUDA device (") + cudaGetErrorString(e) + "); this backend has no CPU fallback");
+    if (device_id < 0 || device_id >= count) return fail(nullptr, SRT_ERR_INVALID, "srt_create: bad device ordinal");
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) return fail(nullptr, SRT_ERR_CUDA, "cudaGetDeviceProperties failed");
+    if (prop.major < 10)
+        return fail(nullptr, SRT_ERR_NO_DEVICE, std::string("srt_create: device '") + prop.name + "' is not sm_100 class; kernels are built for sm_100a only");
+    srt_backend *b = new srt_backend();
+    b->device = device_id;
+    b->sm_count = prop.multiProcessorCount;
+    b->clock_khz = prop.clockRate;
+    b->max_smem_optin = prop.sharedMemPerBlockOptin;
+    *out = b;
+    SRT_CUDA(b, cudaSetDevice(device_id));
+    SRT_CUDA(b, cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+    SRT_CUDA(b, cudaEventCreate(&b->ev_start));
+    SRT_CUDA(b, cudaEventCreate(&b->ev_stop));
+    SRT_CUDA(b, cudaMalloc(&b->d_counters, 16));
+    SRT_CUDA(b, cudaMemset(b->d_counters, 0, 16));
+    SRT_CUDA(b, cudaMallocHost(&b->h_rays, sizeof(unsigned long long)));
+    *b->h_rays = 0;
+    return SRT_OK;
+}
+
+void srt_destroy(srt_backend *b) {
+    if (!b) return;
+    cudaSetDevice(b->device);
+    if (b->stream) cudaStreamSynchronize(b->stream);
+    cudaFree(b->d_spheres); cudaFree(b->d_materials);
+    cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
+    cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
+    cudaFree(b->d_counters);
+    if (b->h_rays) cudaFreeHost(b->h_rays);
+    if (b->ev_start) cudaEventDestroy(b->ev_start);
+    if (b->ev_stop) cudaEventDestroy(b->ev_stop);
+    if (b->stream) cudaStreamDestroy(b->stream);
+    delete b;
+}
+
+static int drain(srt_backend *b) {
+    if (b->in_flight) {
+        SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+        b->in_flight = false;
+    }
+    return SRT_OK;
+}
+
+int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres, const srt_scene_options *options) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!spheres || n_spheres == 0 || !options) return fail(b, SRT_ERR_INVALID, "srt_set_scene: null/empty scene");
+    if (options->lane_width != 1 && options->lane_width != 4 && options->lane_width != 8)
+        return fail(b, SRT_ERR_INVALID, "srt_set_scene: lane_width must be 1, 4 or 8");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    int rc = drain(b);
+    if (rc) return rc;
+    const uint32_t n_pad = (n_spheres + 7u) & ~7u;
+    if ((size_t)n_pad * sizeof(float4) > b->max_smem_optin)
+        return fail(b, SRT_ERR_TOO_LARGE, "srt_set_scene: scene exceeds the shared-memory resident limit");
+    std::vector<float4> sph(n_pad, make_float4(0.f, 0.f, 0.f, 0.f));   // zero spheres: d2 < 0 never holds
+    std::vector<DevMaterial> mats(n_pad);
+    memset(mats.data(), 0, mats.size() * sizeof(DevMaterial));
+    for (uint32_t i = 0; i < n_spheres; ++i) {
+        const srt_sphere &s = spheres[i];
+        const volatile float r = s.radius;
+        const volatile float r2 = r * r;                                  // main.cpp:406, one IEEE f32 multiply
+        sph[i] = make_float4(s.position[0], s.position[1], s.position[2], r2);
+        const srt_material &m = s.material;
+        mats[i].color_spec = make_float4(m.color[0], m.color[1], m.color[2], m.specular);
+        mats[i].emis_ior = make_float4(m.emissive[0], m.emissive[1], m.emissive[2], m.index_of_refraction);
+        const float oms = (float)(1.0 - (double)m.specular);              // main.cpp:463
+        const volatile float one = 1.0f;
+        const volatile float inv_ior = one / m.index_of_refraction;       // main.cpp:466 (inf when IOR == 0: unused)
+        mats[i].derived = make_float4(oms, inv_ior, 0.f, 0.f);
+    }
+    cudaFree(b->d_spheres); b->d_spheres = nullptr;
+    cudaFree(b->d_materials); b->d_materials = nullptr;
+    SRT_CUDA(b, cudaMalloc(&b->d_spheres, sph.size() * sizeof(float4)));
+    SRT_CUDA(b, cudaMalloc(&b->d_materials, mats.size() * sizeof(DevMaterial)));
+    SRT_CUDA(b, cudaMemcpy(b->d_spheres, sph.data(), sph.size() * sizeof(float4), cudaMemcpyHostToDevice));
+    SRT_CUDA(b, cudaMemcpy(b->d_materials, mats.data(), mats.size() * sizeof(DevMaterial), cudaMemcpyHostToDevice));
+    b->n_spheres = n_spheres;
+    b->n_pad = n_pad;
+    b->opt = *options;
+    return SRT_OK;
+}
+
+int srt_reset_accumulation(srt_backend *b) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_reset_accumulation: no image (call srt_resize)");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    const size_t n = (size_t)b->width * b->height;
+    SRT_CUDA(b, cudaMemsetAsync(b->d_accum, 0, n * sizeof(float4), b->stream));
+    SRT_CUDA(b, cudaMemsetAsync(b->d_rgba, 0, n * sizeof(uint32_t), b->stream));
+    b->tap_valid = false;
+    return SRT_OK;
+}
+
+int srt_resize(srt_backend *b, uint32_t width, uint32_t height) {
+    if (!b) return SRT_ERR_INVALID;
+    if (width == 0 || height == 0) return fail(b, SRT_ERR_INVALID, "srt_resize: zero size");
+    if ((uint64_t)width * height > 0x7FFFFFFFull) return fail(b, SRT_ERR_TOO_LARGE, "srt_resize: image too large");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    int rc = drain(b);
+    if (rc) return rc;
+    const size_t n = (size_t)width * height;
+    if (width != b->width || height != b->height || !b->d_accum_own) {
+        cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own); cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
+        b->d_accum_own = nullptr; b->d_rgba_own = nullptr; b->d_tap_prim = nullptr; b->d_tap_t = nullptr;
+        SRT_CUDA(b, cudaMalloc(&b->d_accum_own, n * sizeof(float4)));
+        SRT_CUDA(b, cudaMalloc(&b->d_rgba_own, n * sizeof(uint32_t)));
+        b->width = width;
+        b->height = height;
+    }
+    b->d_accum = b->d_accum_own;
+    b->d_rgba = b->d_rgba_own;
+    return srt_reset_accumulation(b);
+}
+
+int srt_bind_device_buffers(srt_backend *b, void *accum_dev, void *rgba_dev) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!b->d_accum_own) return fail(b, SRT_ERR_INVALID, "srt_bind_device_buffers: call srt_resize first");
+    int rc = drain(b);
+    if (rc) return rc;
+    b->d_accum = accum_dev ? (float4 *)accum_dev : b->d_accum_own;
+    b->d_rgba = rgba_dev ? (uint32_t *)rgba_dev : b->d_rgba_own;
+    return SRT_OK;
+}
+
+int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *args) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!cam || !args) return fail(b, SRT_ERR_INVALID, "srt_render: null argument");
+    if (!b->d_spheres) return fail(b, SRT_ERR_INVALID, "srt_render: no scene (call srt_set_scene)");
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_render: no image (call srt_resize)");
+    if (args->n_samples == 0 || args->sample_stride == 0) return fail(b, SRT_ERR_INVALID, "srt_render: n_samples and sample_stride must be >= 1");
+    if (args->accum_mode != SRT_ACCUM_MEAN && args->accum_mode != SRT_ACCUM_SUM) return fail(b, SRT_ERR_INVALID, "srt_render: bad accum_mode");
+    if (args->accum_mode == SRT_ACCUM_MEAN && args->sample_stride != 1)
+        return fail(b, SRT_ERR_INVALID, "srt_render: the exact running mean needs contiguous samples (sample_stride == 1)");
+    if ((uint64_t)args->first_sample + (uint64_t)args->n_samples * args->sample_stride > 0xFFFFFFFFull)
+        return fail(b, SRT_ERR_INVALID, "srt_render: sample index overflows 32 bits");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    int rc = drain(b);
+    if (rc) return rc;
+
+    KernelParams P;
+    memset(&P, 0, sizeof(P));
+    P.spheres = b->d_spheres;
+    P.materials = b->d_materials;
+    P.n_pad = b->n_pad;
+    P.n_spheres = b->n_spheres;
+    P.use_sky = b->opt.use_sky_color;
+    for (int i = 0; i < 3; ++i) {
+        P.cam.pos[i] = cam->camera_position[i];
+        P.cam.x[i] = cam->camera_x[i];
+        P.cam.y[i] = cam->camera_y[i];
+        P.cam.film_center[i] = cam->film_center[i];
+    }
+    P.cam.film_w = cam->film_w;
+    P.cam.film_h = cam->film_h;
+    P.width = b->width;
+    P.height = b->height;
+    P.blocks_x = (b->width + 7u) / 8u;
+    P.total_items = P.blocks_x * ((b->height + 3u) / 4u) * 32u;
+    P.first_sample = args->first_sample;
+    P.n_samples = args->n_samples;
+    P.sample_stride = args->sample_stride;
+    P.accum_mode = args->accum_mode;
+    P.stream_base = args->stream_base;
+    P.accum = b->d_accum;
+    P.rgba = b->d_rgba;
+    if (args->record_primary) {
+        const size_t n = (size_t)b->width * b->height;
+        if (!b->d_tap_prim) {
+            SRT_CUDA(b, cudaMalloc(&b->d_tap_prim, n * sizeof(uint32_t)));
+            SRT_CUDA(b, cudaMalloc(&b->d_tap_t, n * sizeof(float)));
+        }
+        P.tap_prim = b->d_tap_prim;
+        P.tap_t = b->d_tap_t;
+        b->tap_valid = true;
+    }
+    P.rays = (unsigned long long *)b->d_counters;
+    P.work_counter = (unsigned int *)(b->d_counters + 8);
+
+    render_kernel_t kernel = pick_kernel(b->opt);
+    const size_t smem = (size_t)b->n_pad * sizeof(float4);
+    SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockThreads, smem));
+    if (per_sm < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
+    uint32_t grid = (uint32_t)(b->sm_count * per_sm);                 // persistent: one resident wave
+    const uint32_t max_useful = (P.total_items + kBlockThreads - 1) / kBlockThreads;
+    if (grid > max_useful) grid = max_useful;
+
+    SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 16, b->stream));
+    SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
+    kernel<<<grid, kBlockThreads, smem, b->stream>>>(P);
+    SRT_CUDA(b, cudaGetLastError());
+    SRT_CUDA(b, cudaEventRecord(b->ev_stop, b->stream));
+    SRT_CUDA(b, cudaMemcpyAsync(b->h_rays, b->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, b->stream));
+    b->launches += 1;
+    b->in_flight = true;
+    return SRT_OK;
+}
+
+int srt_poll(srt_backend *b) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!b->in_flight) return 1;
+    cudaError_t e = cudaStreamQuery(b->stream);
+    if (e == cudaSuccess) return 1;
+    if (e == cudaErrorNotReady) return 0;
+    return fail(b, SRT_ERR_CUDA, std::string("srt_poll: ") + cudaGetErrorString(e));
+}
+
+int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays) {
+    if (!b) return SRT_ERR_INVALID;
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+    b->in_flight = false;
+    if (out_ms) {
+        float ms = 0.f;
+        if (b->launches) SRT_CUDA(b, cudaEventElapsedTime(&ms, b->ev_start, b->ev_stop));
+        *out_ms = ms;
+    }
+    if (out_rays) *out_rays = *b->h_rays;
+    return SRT_OK;
+}
+
+int srt_resolve_sum(srt_backend *b, uint32_t total_samples) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!b->d_accum || total_samples == 0) return fail(b, SRT_ERR_INVALID, "srt_resolve_sum: no image or zero samples");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    const uint32_t n = b->width * b->height;
+    const volatile float one = 1.0f;
+    const float inv_n = one / (float)total_samples;
+    resolve_sum_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->d_rgba, n, inv_n);
+    SRT_CUDA(b, cudaGetLastError());
+    b->launches += 1;
+    b->in_flight = true;
+    return SRT_OK;
+}
+
+int srt_read_rgba8(srt_backend *b, void *dst) {
+    if (!b || !dst) return SRT_ERR_INVALID;
+    if (!b->d_rgba) return fail(b, SRT_ERR_INVALID, "srt_read_rgba8: no image");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    SRT_CUDA(b, cudaMemcpyAsync(dst, b->d_rgba, (size_t)b->width * b->height * 4, cudaMemcpyDeviceToHost, b->stream));
+    SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+    b->in_flight = false;
+    return SRT_OK;
+}
+
+int srt_read_accum(srt_backend *b, float *dst) {
+    if (!b || !dst) return SRT_ERR_INVALID;
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_read_accum: no image");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    SRT_CUDA(b, cudaMemcpyAsync(dst, b->d_accum, (size_t)b->width * b->height * 16, cudaMemcpyDeviceToHost, b->stream));
+    SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+    b->in_flight = false;
+    return SRT_OK;
+}
+
+int srt_read_primary(srt_backend *b, uint32_t *prim, float *t) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!b->tap_valid) return fail(b, SRT_ERR_INVALID, "srt_read_primary: no render with record_primary since the last reset");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    const size_t n = (size_t)b->width * b->height;
+    if (prim) SRT_CUDA(b, cudaMemcpyAsync(prim, b->d_tap_prim, n * 4, cudaMemcpyDeviceToHost, b->stream));
+    if (t) SRT_CUDA(b, cudaMemcpyAsync(t, b->d_tap_t, n * 4, cudaMemcpyDeviceToHost, b->stream));
+    SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+    b->in_flight = false;
+    return SRT_OK;
+}
+
+void *srt_accum_device_ptr(srt_backend *b) { return b ? (void *)b->d_accum : nullptr; }
+void *srt_rgba_device_ptr(srt_backend *b) { return b ? (void *)b->d_rgba : nullptr; }
+void *srt_cuda_stream(srt_backend *b) { return b ? (void *)b->stream : nullptr; }
+
+int srt_device_info(srt_backend *b, int *sm_count, int *clock_khz, uint64_t *launches) {
+    if (!b) return SRT_ERR_INVALID;
+    if (sm_count) *sm_count = b->sm_count;
+    if (clock_khz) *clock_khz = b->clock_khz;
+    if (launches) *launches = b->launches;
+    return SRT_OK;
+}
+
+} // extern "C"

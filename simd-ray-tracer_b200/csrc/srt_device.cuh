@@ -1,0 +1,238 @@
+// srt_device.cuh -- device-side arithmetic of the path-tracing hot path (sm_100a).
+//
+// Every floating-point operation that reaches the image is written with an explicit
+// round-to-nearest intrinsic (__fadd_rn / __fmul_rn / __fdiv_rn / __fsqrt_rn), which nvcc
+// never contracts into FMA, and the file is compiled with -fmad=false on top of that.
+// __fmaf_rn appears exactly where the reference's AVX2 profile has _mm256_fmadd_ps
+// (x64_math.h:409-420) and nowhere else.  That is what makes images bit-identical to the
+// reference's CPU path under the per-path RNG stream contract.
+//
+// Citations are file:line in the reference (Ne0nWinds/SIMD-Ray-Tracer).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace srt {
+
+constexpr float kEps = 1e-4f;   // F32Epsilon base.h:889
+constexpr float kMax = 1e30f;   // F32Max     base.h:891
+constexpr int kMaxBounce = 5;   // MaxRayBounce main.cpp:387
+
+struct f3 { float x, y, z; };
+
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 add3(f3 a, f3 b) { return mk3(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 sub3(f3 a, f3 b) { return mk3(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y), __fsub_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 mul3(f3 a, f3 b) { return mk3(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y), __fmul_rn(a.z, b.z)); }
+__device__ __forceinline__ f3 scale3(float s, f3 a) { return mk3(__fmul_rn(s, a.x), __fmul_rn(s, a.y), __fmul_rn(s, a.z)); }
+__device__ __forceinline__ f3 neg3(f3 a) { return mk3(-a.x, -a.y, -a.z); }   // sign flip, x64_math.h:219-222
+// v3::Dot x64_math.h:224-227: mul,mul,mul then (x+y)+z
+__device__ __forceinline__ float dot3(f3 a, f3 b) {
+    return __fadd_rn(__fadd_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)), __fmul_rn(a.z, b.z));
+}
+// v3::Normalize x64_math.h:234-245 (NormalizeFast == Normalize, wasm_math.h:168-170)
+__device__ __forceinline__ f3 normalize3(f3 a) {
+    const float lsq = dot3(a, a);
+    if (!(lsq > kEps)) return mk3(0.0f, 0.0f, 0.0f);
+    const float len = __fsqrt_rn(lsq);
+    return mk3(__fdiv_rn(a.x, len), __fdiv_rn(a.y, len), __fdiv_rn(a.z, len));
+}
+
+// ---- PRNG: u32_random_state::PCG base.h:954-963, RandomFloat base.h:983-989 ------------
+// InverseMaxInt = (f32)((f64)(Max-Min)/4294967295.0) is exactly 2^-32 for a unit range and
+// 2^-31 for a range of 2 (checked on the host in tests/test_host_logic.py).
+constexpr float kInvU32Range1 = 2.3283064365386963e-10f;   // 2^-32
+constexpr float kInvU32Range2 = 4.6566128730773926e-10f;   // 2^-31
+
+__device__ __forceinline__ uint32_t pcg_next(uint64_t &s) {
+    const uint64_t old = s;
+    s = old * 6364136223846793005ULL + 1442695040888963407ULL;
+    const uint32_t v = (uint32_t)(old >> 32) ^ (uint32_t)old;
+    return __funnelshift_r(v, v, (uint32_t)(old >> 59));    // RotateRight32 x64_math.h:168-170
+}
+__device__ __forceinline__ float rand_float(uint64_t &s, float inv_range, float mn) {
+    return __fadd_rn(__fmul_rn(__uint2float_rn(pcg_next(s)), inv_range), mn);
+}
+// Per-path stream seed: main.cpp:667-676 evaluated on a 64-bit index.
+__host__ __device__ __forceinline__ uint64_t stream_seed(uint64_t i) {
+    uint64_t s = 0x420247153476526ULL * i;
+    s += 0x8442885C91A5C8DULL;
+    s ^= s >> ((7 + i) % 64);
+    s ^= s << 23;
+    s ^= s >> ((0x29 ^ i) % 64);
+    s = (s * 0x11C19226CEB4769AULL) + 0x1105404122082911ULL;
+    s ^= s << 19;
+    s ^= s >> 13;
+    return s;
+}
+
+// ---- Reflectance main.cpp:292-300 ---------------------------------------------------------
+__device__ __forceinline__ float reflectance(float c, float eta) {
+    float r0 = __fdiv_rn(__fsub_rn(1.0f, eta), __fadd_rn(1.0f, eta));
+    r0 = __fmul_rn(r0, r0);
+    float r1 = __fsub_rn(1.0f, c);
+    r1 = __fmul_rn(__fmul_rn(__fmul_rn(__fmul_rn(r1, r1), r1), r1), r1);
+    return __fadd_rn(r0, __fmul_rn(__fsub_rn(1.0f, r0), r1));
+}
+
+// ---- Tonemap + pack main.cpp:312-346 ------------------------------------------------------
+__device__ __forceinline__ float saturate_ref(float v) {   // x64_math.h:97-101 (NaN passes through)
+    if (v < 0.0f) return 0.0f;
+    if (v > 1.0f) return 1.0f;
+    return v;
+}
+__device__ __forceinline__ float linear_to_srgb(float l) {
+    l = saturate_ref(l);
+    if (l < 0.0031308f) return __fmul_rn(l, 12.92f);
+    return __fsqrt_rn(l);
+}
+__device__ __forceinline__ uint32_t to_u8(float v) {
+    const float s = __fmul_rn(saturate_ref(v), 255.0f);
+    return (uint32_t)__float2int_rz(s) & 0xFFu;             // NaN -> 0, like cvttss2si's low byte
+}
+__device__ __forceinline__ uint32_t pack_rgba8(float r, float g, float b) {
+    return to_u8(linear_to_srgb(r)) | (to_u8(linear_to_srgb(g)) << 8) | (to_u8(linear_to_srgb(b)) << 16) | (255u << 24);
+}
+
+// ---- device-side scene records --------------------------------------------------------------
+// Sphere: float4 {cx, cy, cz, r*r}.  r*r is the reference's own f32 product (main.cpp:406),
+// taken once at upload instead of once per test; the radius itself is never used again.
+struct DevMaterial {
+    float4 color_spec;   // Color.xyz, Specular
+    float4 emis_ior;     // Emissive.xyz, IndexOfRefraction
+    float4 derived;      // x = (f32)(1.0 - (f64)Specular) (main.cpp:463), y = 1.0f / IOR (main.cpp:466)
+};
+
+struct DevCamera {
+    float pos[3], x[3], y[3], film_center[3];
+    float film_w, film_h;
+};
+
+struct KernelParams {
+    const float4 *spheres;       // n_pad entries, zero spheres as padding (never hit)
+    const DevMaterial *materials;
+    uint32_t n_pad;              // multiple of 8
+    uint32_t n_spheres;          // real sphere count
+    int32_t use_sky;
+    DevCamera cam;
+    uint32_t width, height;
+    uint32_t blocks_x;           // 8x4 pixel blocks per row
+    uint32_t total_items;        // blocks_x * blocks_y * 32
+    uint32_t first_sample, n_samples, sample_stride, accum_mode;
+    uint64_t stream_base;
+    float4 *accum;
+    uint32_t *rgba;
+    uint32_t *tap_prim;          // optional
+    float *tap_t;                // optional
+    unsigned long long *rays;
+    unsigned int *work_counter;
+};
+
+struct Hit {
+    float t;
+    uint32_t prim;
+    bool hit, inside;
+};
+
+// v3x::Dot / LengthSquared of the intersection loop: profile I x64_math.h:299-309,
+// profile F x64_math.h:409-420.
+template <bool FMA>
+__device__ __forceinline__ float lane_dot(float ax, float ay, float az, float bx, float by, float bz) {
+    if (FMA) return __fmaf_rn(az, bz, __fmaf_rn(ay, by, __fmul_rn(ax, bx)));
+    return __fadd_rn(__fadd_rn(__fmul_rn(ax, bx), __fmul_rn(ay, by)), __fmul_rn(az, bz));
+}
+
+// A3 + A4 with SIMD-lane semantics (main.cpp:392-455): sphere s is lane s % W of group
+// s / W.  Every lane keeps its own MinT (strict <), group and sticky inside bit; the winner
+// is the first lane holding the horizontal minimum.  The always-executed part is 15 FP32
+// issue slots (profile F) or 19 (profile I) + 1 compare per test; the rest sits behind the
+// rare `d2 < r2` branch.
+template <int W, bool FMA>
+__device__ __forceinline__ Hit intersect_lanes(const float4 *__restrict__ sph, uint32_t n_pad, f3 o, f3 d) {
+    float min_t[W];
+    uint32_t group[W];
+    uint32_t inside_bits = 0;
+#pragma unroll
+    for (int l = 0; l < W; ++l) { min_t[l] = kMax; group[l] = 0; }
+
+#pragma unroll 1
+    for (uint32_t base = 0; base < n_pad; base += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 s = sph[base + j];                     // warp-uniform LDS.128 broadcast
+            const float scx = __fsub_rn(s.x, o.x), scy = __fsub_rn(s.y, o.y), scz = __fsub_rn(s.z, o.z);   // :401
+            const float t = lane_dot<FMA>(scx, scy, scz, d.x, d.y, d.z);                                  // :402
+            const float vx = __fsub_rn(scx, __fmul_rn(d.x, t));                                          // :403,407
+            const float vy = __fsub_rn(scy, __fmul_rn(d.y, t));
+            const float vz = __fsub_rn(scz, __fmul_rn(d.z, t));
+            const float d2 = lane_dot<FMA>(vx, vy, vz, vx, vy, vz);
+            if (d2 < s.w) {                                                                               // :409
+                constexpr int kLaneMask = W - 1;
+                const int l = j & kLaneMask;                    // static after unrolling
+                const float x = __fsqrt_rn(__fsub_rn(s.w, d2));                                           // :413
+                float it = __fsub_rn(t, x);                                                               // :415
+                const bool test = it < kEps;                                                              // :416
+                if (test) it = __fadd_rn(t, x);                                                           // :417
+                if (it < min_t[l] && it > kEps) {                                                         // :419-421
+                    min_t[l] = it;                                                                        // :427
+                    group[l] = (base + j) / W;                                                            // :426
+                    if (test) inside_bits |= (1u << l);                                                   // :425 sticky
+                }
+            }
+        }
+    }
+    float mv = min_t[0];
+#pragma unroll
+    for (int l = 1; l < W; ++l) mv = (min_t[l] < mv) ? min_t[l] : mv;                                     // HorizontalMin :432
+    Hit h;
+    h.t = mv;
+    h.hit = !(mv == kMax);                                                                                // :433
+    int idx = W - 1;
+#pragma unroll
+    for (int l = W - 2; l >= 0; --l) idx = (min_t[l] == mv) ? l : idx;                                    // FindFirstIndex :441
+    uint32_t g = group[0];
+#pragma unroll
+    for (int l = 1; l < W; ++l) g = (idx == l) ? group[l] : g;
+    h.prim = h.hit ? g * W + (uint32_t)idx : 0xFFFFFFFFu;                                                 // :443
+    h.inside = (inside_bits >> idx) & 1u;                                                                 // :455
+    return h;
+}
+
+// A3 + A4 with RenderTileScalar semantics (main.cpp:541-588): d2 == r2 is a hit, a later
+// sphere wins ties, t == 1e-4 is accepted, inside is overwritten.
+__device__ __forceinline__ Hit intersect_scalar(const float4 *__restrict__ sph, uint32_t n_pad, uint32_t n_real, f3 o, f3 d) {
+    float min_t = kMax;
+    uint32_t prim = 0;
+    bool inside = false;
+#pragma unroll 1
+    for (uint32_t base = 0; base < n_pad; base += 8) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 s = sph[base + j];
+            const float scx = __fsub_rn(s.x, o.x), scy = __fsub_rn(s.y, o.y), scz = __fsub_rn(s.z, o.z);
+            const float t = lane_dot<false>(scx, scy, scz, d.x, d.y, d.z);
+            const float vx = __fsub_rn(scx, __fmul_rn(d.x, t));
+            const float vy = __fsub_rn(scy, __fmul_rn(d.y, t));
+            const float vz = __fsub_rn(scz, __fmul_rn(d.z, t));
+            const float d2 = lane_dot<false>(vx, vy, vz, vx, vy, vz);
+            // `d2 > r2 -> continue` lets NaN through, so padding is excluded by index.
+            if (!(d2 > s.w) && (base + j) < n_real) {                                                                            // :557
+                const float x = __fsqrt_rn(__fsub_rn(s.w, d2));
+                float it = __fsub_rn(t, x);
+                const bool test = it < kEps;
+                if (test) it = __fadd_rn(t, x);
+                if (!(it > min_t) && !(it < kEps)) {                                                      // :568-569
+                    inside = test; prim = base + j; min_t = it;
+                }
+            }
+        }
+    }
+    Hit h;
+    h.t = min_t;
+    h.hit = !(min_t == kMax);
+    h.prim = h.hit ? prim : 0xFFFFFFFFu;
+    h.inside = inside;
+    return h;
+}
+
+} // namespace srt
