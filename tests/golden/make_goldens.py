@@ -1,0 +1,91 @@
+#!/usr/bin/env python3
+"""Generates tests/golden/*.npz|json from the reference's OWN compiled code (oracle/_ref).
+
+Run in the build container (needs /root/reference to have been compiled by
+oracle/build_ref.py):   python tests/golden/make_goldens.py
+The fixtures are committed; /root/reference is never read at test time."""
+import json
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(HERE))
+import orclib  # noqa: E402
+
+W, H, SPP = 48, 27, 2
+MODES = {"w8f": ("w8", 1), "w4i": ("w4", 1), "scalar": ("w4", 0)}   # name -> (lib, EnableSIMD)
+
+
+def main():
+    refs = {"w4": orclib.Ref("w4"), "w8": orclib.Ref("w8")}
+    R = refs["w8"]
+    out = {}
+    # ---- scene tables + cameras ------------------------------------------------------------
+    for s in range(3):
+        sp, sky, hdr = R.scene(s)
+        out[f"scene{s}_spheres"] = sp.view(np.uint8).reshape(len(sp), 80)
+        out[f"scene{s}_sky"] = np.array([int(sky)])
+        out[f"scene{s}_header"] = hdr
+    # ---- images ----------------------------------------------------------------------------
+    for s in range(3):
+        for name, (lib, simd) in MODES.items():
+            r = refs[lib].render(s, W, H, SPP, simd=simd, threads=1, flags=3)
+            for k in ("accum", "rgba", "prim", "t"):
+                out[f"img_s{s}_{name}_{k}"] = r[k]
+            out[f"img_s{s}_{name}_rays"] = np.array([r["rays"]], np.uint64)
+            out[f"img_s{s}_{name}_camera"] = r["camera"]
+    np.savez_compressed(os.path.join(HERE, "ref_goldens.npz"), **out)
+
+    # ---- known-answer vectors ---------------------------------------------------------------
+    import ctypes as C
+    kat = {}
+    seeds = [R.L.srt_ref_thread_seed(i) for i in range(4)] + [0x29D7A0A514F22432, 0xCD46749A57ACB371]
+    kat["thread_seeds"] = [int(x) for x in seeds[:4]]
+    rng = {}
+    for sd in seeds:
+        u = np.zeros(16, np.uint32)
+        R.L.srt_ref_rng(sd, 16, 0.0, 1.0, 0, u.ctypes.data)
+        e = {"pcg": [int(x) for x in u]}
+        for (mn, mx) in [(-1.0, 1.0), (-0.5, 0.5), (0.0, 1.0), (2.0, 5.0), (0.15, 1.0)]:
+            f = np.zeros(16, np.float32)
+            R.L.srt_ref_rng(sd, 16, mn, mx, 1, f.ctypes.data)
+            e[f"float_{mn}_{mx}"] = [int(x) for x in f.view(np.uint32)]
+        rng[str(int(sd))] = e
+    kat["rng"] = rng
+    edge = np.array([0.0, -0.0, -1.0, 1e-9, 0.0031307, 0.0031308, np.nextafter(np.float32(0.0031308), np.float32(1)),
+                     0.0031309, 0.25, 0.5, 0.999999, 1.0, 1.0000001, 2.0, 1e30, np.inf, -np.inf, np.nan], np.float32)
+    kat["srgb_in"] = [int(x) for x in edge.view(np.uint32)]
+    kat["srgb_out"] = [int(np.float32(R.L.srt_ref_linear_to_srgb(float(x))).view(np.uint32)) if not np.isnan(x)
+                       else int(np.float32(R.L.srt_ref_linear_to_srgb(C.c_float(float('nan')))).view(np.uint32)) for x in edge]
+    packs = []
+    for x in edge:
+        v = np.array([x, 0.5, 0.001, 1.0], np.float32)
+        packs.append(int(R.L.srt_ref_pack(v.ctypes.data)))
+    kat["pack_out"] = packs
+    refl = []
+    for c in [0.0, 0.1, 0.5, 0.9, 1.0, -0.2]:
+        for eta in [1.5, 1.0 / 1.5, 1.0, 2.4]:
+            refl.append([c, eta, int(np.float32(R.L.srt_ref_reflectance(c, eta)).view(np.uint32))])
+    kat["reflectance"] = refl
+    norm = []
+    gen = np.random.default_rng(7)
+    vecs = [np.array(v, np.float32) for v in [(0, 0, 0), (0.005, 0.005, 0.005), (0.01, 0, 0), (1, 2, 3), (-4, 0.5, 1e-3), (1e10, 1, 1)]]
+    vecs += [gen.uniform(-1, 1, 3).astype(np.float32) for _ in range(10)]
+    R.L.srt_ref_set_ieee_normalize_fast(1)
+    for v in vecs:
+        o = np.zeros(3, np.float32)
+        R.L.srt_ref_normalize(v.ctypes.data, 0, o.ctypes.data)
+        o2 = np.zeros(3, np.float32)
+        R.L.srt_ref_normalize(v.ctypes.data, 1, o2.ctypes.data)
+        assert o.tobytes() == o2.tobytes()
+        norm.append([[int(x) for x in v.view(np.uint32)], [int(x) for x in o.view(np.uint32)]])
+    kat["normalize"] = norm
+    with open(os.path.join(HERE, "ref_kat.json"), "w") as f:
+        json.dump(kat, f, indent=0)
+    print("wrote goldens:", {k: os.path.getsize(os.path.join(HERE, k)) for k in ("ref_goldens.npz", "ref_kat.json")})
+
+
+if __name__ == "__main__":
+    main()
