@@ -181,3 +181,44 @@ class Backend:
     @property
     def stream_ptr(self):
         return self.L.srt_cuda_stream(self.h)
+
+
+# ---- host mirror (C++): scene tables and camera, no GPU needed ------------------------------
+HOSTLIB_PATH = _build.HOSTLIB
+DRIVER_PATH = _build.DRIVER
+SCENE_SYNTH_1K, SCENE_SYNTH_64K = 3, 4
+_hostlib = None
+
+
+def load_host_library():
+    global _hostlib
+    if _hostlib is None:
+        if not os.path.exists(HOSTLIB_PATH):
+            raise SrtError(f"{HOSTLIB_PATH} is missing: run __graft_entry__.build()")
+        H = C.CDLL(HOSTLIB_PATH)
+        H.srt_host_scene.argtypes = [C.c_uint, C.c_void_p, C.c_uint, C.POINTER(C.c_int), C.c_void_p]
+        H.srt_host_camera.argtypes = [C.c_uint, C.c_float, C.c_float, C.c_float, C.c_uint, C.c_uint, C.c_void_p]
+        _hostlib = H
+    return _hostlib
+
+
+def host_scene(index):
+    """(spheres, use_sky, header) of scene `index` as built by host/srt_scenes.cpp."""
+    H = load_host_library()
+    sky = C.c_int()
+    hdr = np.zeros(6, np.float32)
+    n = H.srt_host_scene(index, None, 0, C.byref(sky), hdr.ctypes.data)
+    if n <= 0:
+        raise SrtError(f"bad scene index {index}")
+    sp = np.zeros(n, sphere_dtype)
+    H.srt_host_scene(index, sp.ctypes.data, n, None, None)
+    return sp, bool(sky.value), hdr
+
+
+def host_camera(index, width, height, header=None):
+    H = load_host_library()
+    if header is None:
+        header = host_scene(index)[2]
+    cam = np.zeros(1, camera_dtype)
+    H.srt_host_camera(index, float(header[3]), float(header[4]), float(header[5]), width, height, cam.ctypes.data)
+    return cam

@@ -13,6 +13,7 @@ CSRC = os.path.join(PKG, "csrc")
 HOST = os.path.join(PKG, "host")
 LIB = os.path.join(PKG, "libsrt_cuda.so")
 DRIVER = os.path.join(PKG, "srt_headless")
+HOSTLIB = os.path.join(PKG, "libsrt_host.so")
 
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-fmad=false",
               "-std=c++17", "-shared", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
@@ -47,15 +48,20 @@ def build_driver(force=False, verbose=False):
         return None
     srcs_all = srcs + [os.path.join(ROOT, "include", "srt_backend.h")]
     if force or _newer(DRIVER, srcs_all) or _newer(DRIVER, [LIB]):
-        cpps = [s for s in srcs if s.endswith(".cpp")]
-        cmd = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-I", os.path.join(ROOT, "include"), *cpps,
-               "-o", DRIVER, "-L", PKG, "-lsrt_cuda", "-Wl,-rpath,$ORIGIN", "-lm", "-pthread"]
-        res = subprocess.run(cmd, capture_output=True, text=True)
-        if verbose or res.returncode != 0:
-            print(" ".join(cmd))
-            print(res.stdout + res.stderr)
-        if res.returncode != 0:
-            raise RuntimeError("g++ failed building srt_headless")
+        common = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-Wall", "-I", os.path.join(ROOT, "include")]
+        link = ["-L", PKG, "-lsrt_cuda", "-Wl,-rpath,$ORIGIN", "-lm", "-pthread"]
+        app = [os.path.join(HOST, f) for f in ("srt_app.cpp", "srt_scenes.cpp")]
+        cmds = [
+            [*common, *app, os.path.join(HOST, "srt_headless.cpp"), "-o", DRIVER, *link],
+            [*common, "-fPIC", "-shared", *app, os.path.join(HOST, "srt_host_capi.cpp"), "-o", HOSTLIB, *link],
+        ]
+        for cmd in cmds:
+            res = subprocess.run(cmd, capture_output=True, text=True)
+            if verbose or res.returncode != 0:
+                print(" ".join(cmd))
+                print(res.stdout + res.stderr)
+            if res.returncode != 0:
+                raise RuntimeError("g++ failed building the host mirror")
     return DRIVER
 
 

@@ -1,0 +1,125 @@
+// srt_headless.cpp -- headless Linux driver: the platform layer of the host mirror.
+//
+// Plays the role of wasm/wasm.cpp / win32/win32.cpp in the reference (main(), the
+// platform-owned `image`, the per-frame OnRender loop and the statistics read-out of
+// wasm/wasm.cpp:176-219) without a window: the presented image goes to a PPM file
+// (rows flipped: the reference's row 0 is the image bottom, GL convention).
+#include "srt_app.h"
+
+#include <algorithm>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <string>
+#include <vector>
+
+static bool WritePpm(const char *Path, const u32 *Pixels, u32 W, u32 H) {
+    FILE *F = fopen(Path, "wb");
+    if (!F) return false;
+    fprintf(F, "P6\n%u %u\n255\n", W, H);
+    std::vector<u8> Row(W * 3);
+    for (u32 y = 0; y < H; ++y) {
+        const u32 *Src = Pixels + (size_t)(H - 1 - y) * W;
+        for (u32 x = 0; x < W; ++x) { Row[x * 3 + 0] = Src[x] & 0xFF; Row[x * 3 + 1] = (Src[x] >> 8) & 0xFF; Row[x * 3 + 2] = (Src[x] >> 16) & 0xFF; }
+        fwrite(Row.data(), 1, Row.size(), F);
+    }
+    fclose(F);
+    return true;
+}
+
+static void Usage() {
+    fprintf(stderr,
+            "usage: srt_headless [--scene 0..4] [--width W] [--height H] [--spp N] [--spf K]\n"
+            "                    [--simd 0|1] [--lanes 4|8] [--fma 0|1] [--device D] [--stream-base B]\n"
+            "                    [--orbit FRAMES] [--out image.ppm] [--accum accum.f32]\n"
+            "  scenes: 0 RGB Glass, 1 Floating Spheres, 2 One Weekend, 3 synthetic 1,024, 4 synthetic 65,536\n"
+            "  --spf: samples per OnRender frame (reference: 1).  --orbit: hold key A for FRAMES frames first.\n");
+}
+
+int main(int argc, char **argv) {
+    u32 Scene = 0, W = 1280, H = 720, Spp = 1, Spf = 1, Orbit = 0;
+    bool Simd = true;
+    backend_params BP;
+    const char *Out = nullptr, *AccumOut = nullptr;
+    for (int i = 1; i < argc; ++i) {
+        std::string A = argv[i];
+        auto Next = [&]() -> const char * { if (i + 1 >= argc) { Usage(); exit(2); } return argv[++i]; };
+        if (A == "--scene") Scene = atoi(Next());
+        else if (A == "--width") W = atoi(Next());
+        else if (A == "--height") H = atoi(Next());
+        else if (A == "--spp") Spp = atoi(Next());
+        else if (A == "--spf") Spf = atoi(Next());
+        else if (A == "--simd") Simd = atoi(Next()) != 0;
+        else if (A == "--lanes") BP.LaneWidth = atoi(Next());
+        else if (A == "--fma") BP.FmaDot = atoi(Next()) != 0;
+        else if (A == "--device") BP.DeviceId = atoi(Next());
+        else if (A == "--stream-base") BP.StreamBase = strtoull(Next(), nullptr, 0);
+        else if (A == "--orbit") Orbit = atoi(Next());
+        else if (A == "--out") Out = Next();
+        else if (A == "--accum") AccumOut = Next();
+        else { Usage(); return 2; }
+    }
+    if (Spf == 0) Spf = 1;
+    if (Spp == 0) Spp = 1;
+    BP.SamplesPerFrame = Spf;
+    SetBackendParams(BP);
+
+    init_params Init = {};
+    if (!OnInit(&Init)) { fprintf(stderr, "OnInit failed: %s\n", LastError()); return 1; }
+
+    std::vector<u32> Present((size_t)W * H);
+    image Image = { Present.data(), W, H, format::R8G8B8A8_U32 };
+    render_params RP = { 0, Simd, Scene };
+
+    // Optional scripted orbit: hold A so every frame resets, like a user dragging the camera.
+    u64 Rays = 0, TotalRays = 0;
+    f64 Ms = 0.0, TotalMs = 0.0;
+    for (u32 f = 0; f < Orbit; ++f) {
+        SetKeyDown(key::A, true);
+        while (!OnRender(Image, RP, &Rays, &Ms) && f != 0) {}
+    }
+    SetKeyDown(key::A, false);
+
+    // Frame loop: (frames + 1) calls publish `frames` frames (SURVEY appendix A protocol).
+    const u32 Frames = (Spp + Spf - 1) / Spf;
+    std::vector<f64> FrameMs;
+    SetKeyDown(key::R, true);                          // start from a clean accumulation
+    const f64 Wall0 = QueryTimestampInMilliseconds();
+    u32 Kicked = 0;
+    bool First = true;
+    while (Kicked < Frames) {
+        const bool Published = OnRender(Image, RP, &Rays, &Ms);
+        if (LastError()[0]) { fprintf(stderr, "OnRender failed: %s\n", LastError()); return 1; }
+        SetKeyDown(key::R, false);
+        if (Published && !First) { FrameMs.push_back(Ms); TotalRays += Rays; TotalMs += Ms; }
+        if (Published || First) { Kicked += 1; First = false; }
+        else WaitForFrame();                           // not ready: block instead of spinning
+    }
+    WaitForFrame();
+    f64 LastMs = 0.0;
+    u64 LastRays = 0;
+    srt_wait(GetBackend(), &LastMs, &LastRays);
+    FrameMs.push_back(LastMs); TotalRays += LastRays; TotalMs += LastMs;
+    srt_read_rgba8(GetBackend(), Present.data());
+    const f64 Wall = QueryTimestampInMilliseconds() - Wall0;
+
+    if (Out && !WritePpm(Out, Present.data(), W, H)) { fprintf(stderr, "cannot write %s\n", Out); return 1; }
+    if (AccumOut) {
+        std::vector<f32> Acc((size_t)W * H * 4);
+        ReadAccumulator(Acc.data());
+        FILE *F = fopen(AccumOut, "wb");
+        if (!F) { fprintf(stderr, "cannot write %s\n", AccumOut); return 1; }
+        fwrite(Acc.data(), sizeof(f32), Acc.size(), F);
+        fclose(F);
+    }
+    std::sort(FrameMs.begin(), FrameMs.end());
+    const f64 P50 = FrameMs[FrameMs.size() / 2], P99 = FrameMs[std::min(FrameMs.size() - 1, (size_t)(FrameMs.size() * 0.99))];
+    const scene *S = GetScene(Scene);
+    printf("{\"scene\": \"%s\", \"spheres\": %u, \"width\": %u, \"height\": %u, \"spp\": %u, \"frames\": %zu, "
+           "\"rays\": %llu, \"device_ms\": %.4f, \"wall_ms\": %.3f, \"mrays_per_s\": %.2f, "
+           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u}\n",
+           S->Name, S->SphereCount, W, H, Frames * Spf, FrameMs.size(), (unsigned long long)TotalRays, TotalMs, Wall,
+           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount());
+    OnShutdown();
+    return 0;
+}
