@@ -65,7 +65,7 @@ typedef struct srt_scene_options {
                                inside flag of main.cpp:419-427); 1: RenderTileScalar */
     int32_t fma_dot;        /* 1: v3x8::Dot/LengthSquared use FMA (x64_math.h:409-420);
                                0: mul,mul,mul,add,add (x64_math.h:299-309) */
-    int32_t _reserved;
+    int32_t _reserved;      /* 0. (non-zero selects diagnostic kernel variants: 1 = scalar-issue loop) */
 } srt_scene_options;
 
 typedef enum {

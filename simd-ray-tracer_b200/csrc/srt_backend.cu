@@ -6,6 +6,7 @@
 // when there is no usable device.
 #include "../../include/srt_backend.h"
 #include "srt_device.cuh"
+#include "srt_packed.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -41,8 +42,8 @@ __device__ __forceinline__ bool item_to_pixel(const KernelParams &P, uint32_t it
 // first_sample > 0, 16 B + 4 B written).  The scene SoA sits in shared memory and is read
 // with warp-uniform LDS.128 broadcasts.
 // ------------------------------------------------------------------------------------------
-template <int W, bool FMA>
-__global__ void __launch_bounds__(kBlockThreads)
+template <int W, bool FMA, bool PACKED, int PAIRS = 4, int MINB = 1>
+__global__ void __launch_bounds__(kBlockThreads, MINB)
 render_paths(const __grid_constant__ KernelParams P) {
     extern __shared__ float4 s_spheres[];
     for (uint32_t i = threadIdx.x; i < P.n_pad; i += blockDim.x) s_spheres[i] = P.spheres[i];
@@ -63,55 +64,62 @@ render_paths(const __grid_constant__ KernelParams P) {
 
     for (;;) {
         // ---- regenerate: finish pixels, fetch new ones, start new paths -------------------
-        bool need = !active && !done && (k == k_end);
-        if (need && pix != kInvalidPixel) {
-            // A8 result + A9 tonemap/pack, main.cpp:484-492
-            P.accum[pix] = make_float4(mean.x, mean.y, mean.z, 1.0f);
-            if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mean.x, mean.y, mean.z);
-            pix = kInvalidPixel;
-        }
-        unsigned m = __ballot_sync(0xFFFFFFFFu, need);
-        while (m) {
-            const unsigned leader = __ffs(m) - 1;
-            unsigned base = 0;
-            if (lane == leader) base = atomicAdd(P.work_counter, __popc(m));
-            base = __shfl_sync(0xFFFFFFFFu, base, leader);
-            if (need) {
-                const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
-                if (item >= P.total_items) { done = true; need = false; }
-                else if (item_to_pixel(P, item, px, py)) {
-                    pix = py * P.width + px;
-                    k = P.first_sample;
-                    need = false;
-                    if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) {
-                        const float4 prev = P.accum[pix];
-                        mean = mk3(prev.x, prev.y, prev.z);
-                    } else {
-                        mean = mk3(0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1) with a zeroed arena
+        // Starting a path costs ~150 issue slots for the whole warp however few lanes need
+        // it, so idle lanes wait until `regen_threshold` of them have gathered (1 for large
+        // scenes, where an idle lane in the intersection loop is the bigger waste).
+        const unsigned idle_mask = __ballot_sync(0xFFFFFFFFu, !active && !done);
+        const unsigned active_mask = __ballot_sync(0xFFFFFFFFu, active);
+        if (idle_mask != 0u && ((uint32_t)__popc(idle_mask) >= P.regen_threshold || active_mask == 0u)) {
+            bool need = !active && !done && (k == k_end);
+            if (need && pix != kInvalidPixel) {
+                // A8 result + A9 tonemap/pack, main.cpp:484-492
+                P.accum[pix] = make_float4(mean.x, mean.y, mean.z, 1.0f);
+                if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mean.x, mean.y, mean.z);
+                pix = kInvalidPixel;
+            }
+            unsigned m = __ballot_sync(0xFFFFFFFFu, need);
+            while (m) {
+                const unsigned leader = __ffs(m) - 1;
+                unsigned base = 0;
+                if (lane == leader) base = atomicAdd(P.work_counter, __popc(m));
+                base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                if (need) {
+                    const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
+                    if (item >= P.total_items) { done = true; need = false; }
+                    else if (item_to_pixel(P, item, px, py)) {
+                        pix = py * P.width + px;
+                        k = P.first_sample;
+                        need = false;
+                        if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) {
+                            const float4 prev = P.accum[pix];
+                            mean = mk3(prev.x, prev.y, prev.z);
+                        } else {
+                            mean = mk3(0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1) with a zeroed arena
+                        }
                     }
                 }
+                m = __ballot_sync(0xFFFFFFFFu, need);
             }
-            m = __ballot_sync(0xFFFFFFFFu, need);
-        }
-        if (!active && !done) {
-            // A1 primary ray, main.cpp:375-385; stream contract: SURVEY 8c P10
-            rng = stream_seed(P.stream_base + (uint64_t)k * plane + pix);
-            atten = mk3(1.0f, 1.0f, 1.0f);
-            out = mk3(0.0f, 0.0f, 0.0f);
-            const float jx = rand_float(rng, kInvU32Range1, -0.5f);
-            const float jy = rand_float(rng, kInvU32Range1, -0.5f);
-            const float film_x = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)px, jx), 2.0f), (float)P.width));
-            const float film_y = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)py, jy), 2.0f), (float)P.height));
-            const float ax = __fmul_rn(__fmul_rn(film_x, P.cam.film_w), 0.5f);
-            const float ay = __fmul_rn(__fmul_rn(film_y, P.cam.film_h), 0.5f);
-            const f3 cam_x = mk3(P.cam.x[0], P.cam.x[1], P.cam.x[2]);
-            const f3 cam_y = mk3(P.cam.y[0], P.cam.y[1], P.cam.y[2]);
-            const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
-            const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
-            o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
-            d = normalize3(sub3(film_p, o));
-            bounce = 0;
-            active = true;
+            if (!active && !done) {
+                // A1 primary ray, main.cpp:375-385; stream contract: SURVEY 8c P10
+                rng = stream_seed(P.stream_base + (uint64_t)k * plane + pix);
+                atten = mk3(1.0f, 1.0f, 1.0f);
+                out = mk3(0.0f, 0.0f, 0.0f);
+                const float jx = rand_float(rng, kInvU32Range1, -0.5f);
+                const float jy = rand_float(rng, kInvU32Range1, -0.5f);
+                const float film_x = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)px, jx), 2.0f), (float)P.width));
+                const float film_y = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)py, jy), 2.0f), (float)P.height));
+                const float ax = __fmul_rn(__fmul_rn(film_x, P.cam.film_w), 0.5f);
+                const float ay = __fmul_rn(__fmul_rn(film_y, P.cam.film_h), 0.5f);
+                const f3 cam_x = mk3(P.cam.x[0], P.cam.x[1], P.cam.x[2]);
+                const f3 cam_y = mk3(P.cam.y[0], P.cam.y[1], P.cam.y[2]);
+                const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
+                const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
+                o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+                d = normalize3(sub3(film_p, o));
+                bounce = 0;
+                active = true;
+            }
         }
         if (__all_sync(0xFFFFFFFFu, done)) break;
 
@@ -120,6 +128,7 @@ render_paths(const __grid_constant__ KernelParams P) {
             rays += 1;                                                    // main.cpp:390
             Hit h;
             if (W == 1) h = intersect_scalar(s_spheres, P.n_pad, P.n_spheres, o, d);
+            else if (PACKED) h = intersect_lanes_packed<(W == 1 ? 4 : W), FMA, PAIRS>(s_spheres, P.n_pad, o, d, P.neg_one, P.one);
             else h = intersect_lanes<(W == 1 ? 4 : W), FMA>(s_spheres, P.n_pad, o, d);
             if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
                 P.tap_t[pix] = h.t;
@@ -143,7 +152,7 @@ render_paths(const __grid_constant__ KernelParams P) {
                 out = add3(out, mul3(mk3(ei.x, ei.y, ei.z), atten));
                 atten = mul3(atten, mk3(cs.x, cs.y, cs.z));
                 // winner's HitNormal / NextRayOrigin, recomputed with the ops of main.cpp:423-429
-                const float4 s = s_spheres[h.prim];
+                const float4 s = PACKED ? paired_sphere(s_spheres, h.prim) : s_spheres[h.prim];
                 const f3 sc = sub3(mk3(s.x, s.y, s.z), o);
                 const f3 ip = scale3(h.t, d);
                 o = add3(o, ip);
@@ -219,8 +228,11 @@ struct srt_backend {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
     // scene
-    float4 *d_spheres = nullptr;
+    float4 *d_spheres = nullptr;         // {cx,cy,cz,r2} per sphere (scalar-issue kernels)
+    float4 *d_spheres2 = nullptr;        // sphere-pair layout (packed f32x2 kernels)
     DevMaterial *d_materials = nullptr;
+    int variant = 0;                     // 0: packed f32x2 loop; 1: scalar-issue loop (diagnostic)
+    uint32_t regen_threshold = 1;
     uint32_t n_spheres = 0, n_pad = 0;
     srt_scene_options opt = {0, 8, 1, 0};
     // images
@@ -252,10 +264,24 @@ static int fail(srt_backend *b, int code, const std::string &msg) {
     } while (0)
 
 typedef void (*render_kernel_t)(const KernelParams);
-static render_kernel_t pick_kernel(const srt_scene_options &o) {
-    if (o.lane_width == 1) return render_paths<1, false>;
-    if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true> : render_paths<4, false>;
-    return o.fma_dot ? render_paths<8, true> : render_paths<8, false>;
+static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed, int variant) {
+    if (variant >= 2 && o.lane_width == 8 && o.fma_dot) {     // tuning experiments (W=8, FMA only)
+        switch (variant) {
+            case 2: return render_paths<8, true, true, 4, 3>;
+            case 3: return render_paths<8, true, true, 2, 3>;
+            case 4: return render_paths<8, true, true, 2, 4>;
+            case 5: return render_paths<8, true, true, 4, 4>;
+            case 6: return render_paths<8, true, true, 1, 4>;
+            default: break;
+        }
+    }
+    if (o.lane_width == 1) return render_paths<1, false, false>;
+    if (packed) {
+        if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, true> : render_paths<4, false, true>;
+        return o.fma_dot ? render_paths<8, true, true> : render_paths<8, false, true>;
+    }
+    if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, false> : render_paths<4, false, false>;
+    return o.fma_dot ? render_paths<8, true, false> : render_paths<8, false, false>;
 }
 
 extern "C" {
@@ -296,7 +322,7 @@ void srt_destroy(srt_backend *b) {
     if (!b) return;
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
-    cudaFree(b->d_spheres); cudaFree(b->d_materials);
+    cudaFree(b->d_spheres); cudaFree(b->d_spheres2); cudaFree(b->d_materials);
     cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
     cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
     cudaFree(b->d_counters);
@@ -342,15 +368,34 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
         const volatile float inv_ior = one / m.index_of_refraction;       // main.cpp:466 (inf when IOR == 0: unused)
         mats[i].derived = make_float4(oms, inv_ior, 0.f, 0.f);
     }
+    std::vector<float4> sph2(n_pad);                                     // pair layout, srt_packed.cuh
+    for (uint32_t p = 0; p < n_pad / 2; ++p) {
+        const float4 &e = sph[2 * p], &o = sph[2 * p + 1];
+        sph2[2 * p] = make_float4(e.x, o.x, e.y, o.y);
+        sph2[2 * p + 1] = make_float4(e.z, o.z, e.w, o.w);
+    }
     cudaFree(b->d_spheres); b->d_spheres = nullptr;
+    cudaFree(b->d_spheres2); b->d_spheres2 = nullptr;
     cudaFree(b->d_materials); b->d_materials = nullptr;
     SRT_CUDA(b, cudaMalloc(&b->d_spheres, sph.size() * sizeof(float4)));
+    SRT_CUDA(b, cudaMalloc(&b->d_spheres2, sph2.size() * sizeof(float4)));
+    SRT_CUDA(b, cudaMemcpy(b->d_spheres2, sph2.data(), sph2.size() * sizeof(float4), cudaMemcpyHostToDevice));
     SRT_CUDA(b, cudaMalloc(&b->d_materials, mats.size() * sizeof(DevMaterial)));
     SRT_CUDA(b, cudaMemcpy(b->d_spheres, sph.data(), sph.size() * sizeof(float4), cudaMemcpyHostToDevice));
     SRT_CUDA(b, cudaMemcpy(b->d_materials, mats.data(), mats.size() * sizeof(DevMaterial), cudaMemcpyHostToDevice));
     b->n_spheres = n_spheres;
     b->n_pad = n_pad;
     b->opt = *options;
+    b->variant = options->_reserved;
+    if (const char *v = getenv("SRT_KERNEL_VARIANT")) b->variant = atoi(v);
+    // Path start-up costs the whole warp ~200 issue slots however few lanes need it.  For
+    // tiny scenes (intersection pass cheaper than that) a warp therefore refills only once
+    // all its lanes are idle, which also keeps its primary rays coherent; measured on B200:
+    // scene 0 (5 spheres) 2.11 ms with 32 vs 2.43 ms with 1; 256+ spheres: 1 is best.
+    b->regen_threshold = n_pad <= 16 ? 32u : (n_pad <= 32 ? 8u : 1u);
+    if (const char *t = getenv("SRT_REGEN_THRESHOLD")) b->regen_threshold = (uint32_t)atoi(t);
+    if (b->regen_threshold < 1) b->regen_threshold = 1;
+    if (b->regen_threshold > 32) b->regen_threshold = 32;
     return SRT_OK;
 }
 
@@ -413,7 +458,11 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
 
     KernelParams P;
     memset(&P, 0, sizeof(P));
-    P.spheres = b->d_spheres;
+    const bool packed = (b->variant != 1) && b->opt.lane_width != 1;
+    P.spheres = packed ? b->d_spheres2 : b->d_spheres;
+    P.regen_threshold = b->regen_threshold;
+    P.neg_one = -1.0f;
+    P.one = 1.0f;
     P.materials = b->d_materials;
     P.n_pad = b->n_pad;
     P.n_spheres = b->n_spheres;
@@ -450,7 +499,7 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     P.rays = (unsigned long long *)b->d_counters;
     P.work_counter = (unsigned int *)(b->d_counters + 8);
 
-    render_kernel_t kernel = pick_kernel(b->opt);
+    render_kernel_t kernel = pick_kernel(b->opt, packed, b->variant);
     const size_t smem = (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;

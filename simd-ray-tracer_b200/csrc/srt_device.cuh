@@ -109,7 +109,8 @@ struct DevCamera {
 };
 
 struct KernelParams {
-    const float4 *spheres;       // n_pad entries, zero spheres as padding (never hit)
+    const float4 *spheres;       // n_pad entries {cx,cy,cz,r2}, zero spheres as padding (never hit);
+                                 // packed kernels: pair layout {x0,x1,y0,y1},{z0,z1,r2_0,r2_1}
     const DevMaterial *materials;
     uint32_t n_pad;              // multiple of 8
     uint32_t n_spheres;          // real sphere count
@@ -126,6 +127,8 @@ struct KernelParams {
     float *tap_t;                // optional
     unsigned long long *rays;
     unsigned int *work_counter;
+    uint32_t regen_threshold;    // start new paths once this many lanes of a warp are idle
+    float neg_one, one;          // -1.0f / +1.0f, deliberately opaque to the compiler (srt_packed.cuh)
 };
 
 struct Hit {
