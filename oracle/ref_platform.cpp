@@ -379,4 +379,35 @@ void srt_ref_normalize(const float *in, int fast, float *out) {              // 
 }
 void srt_ref_set_ieee_normalize_fast(int on) { SrtRefIEEENormalizeFast = on != 0; }
 
+// Replace built-in scene `slot` (0..2) by a caller-supplied sphere table so that the
+// reference's own RenderTile / RenderTileScalar can be timed and checked on the synthetic
+// stress scenes (BASELINE.json configs 3 and 5).  Builds the SoA exactly like the reference
+// does (ConvertScalarSpheresToSIMDSpheres, main.cpp:73-91); padding lanes are zero spheres.
+// header = LookAt.xyz, DefaultDistanceFromLookAt, DefaultXAngle, DefaultYHeight.
+int srt_ref_set_scene(int slot, const void *spheres, uint32_t n, int use_sky, const float *header) {
+    if (!SrtRefInitDone) srt_ref_init(0);
+    if (slot < 0 || slot > 2 || !spheres || n == 0 || !header) return -1;
+    WorkQueueWaitUntilCompletion();
+    scene &S = Scenes[slot];
+    u32 Groups = (n + (SIMD_WIDTH - 1)) / SIMD_WIDTH;
+    void *A = 0, *B = 0, *C = 0;
+    if (posix_memalign(&A, 64, (size_t)n * sizeof(scalar_sphere))) return -2;
+    if (posix_memalign(&B, 64, (size_t)Groups * sizeof(sphere_group))) return -2;
+    if (posix_memalign(&C, 64, (size_t)(n + 1) * sizeof(material))) return -2;
+    memcpy(A, spheres, (size_t)n * sizeof(scalar_sphere));
+    memset(B, 0, (size_t)Groups * sizeof(sphere_group));
+    memset(C, 0, (size_t)(n + 1) * sizeof(material));
+    S.ScalarSpheres.Data = (scalar_sphere *)A; S.ScalarSpheres.Count = n;
+    S.SIMDSpheres.Data = (sphere_group *)B; S.SIMDSpheres.Count = Groups;
+    S.Materials.Data = (material *)C; S.Materials.Count = n + 1;
+    S.UseSkyColor = use_sky != 0;
+    S.LookAt = v3(header[0], header[1], header[2]);
+    S.DefaultDistanceFromLookAt = header[3];
+    S.DefaultXAngle = header[4];
+    S.DefaultYHeight = header[5];
+    ConvertScalarSpheresToSIMDSpheres(&S);
+    SceneIndex = (u32)-1;      // force the scene-switch branch (main.cpp:718-727) on the next frame
+    return 0;
+}
+
 } // extern "C"

@@ -118,6 +118,7 @@ class Ref:
         L.srt_ref_reflectance.restype = C.c_float
         L.srt_ref_reflectance.argtypes = [C.c_float, C.c_float]
         L.srt_ref_normalize.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.srt_ref_set_scene.argtypes = [C.c_int, C.c_void_p, C.c_uint32, C.c_int, C.c_void_p]
         self.threads = L.srt_ref_init(max_threads)
         self.width = L.srt_ref_simd_width()
 
@@ -129,6 +130,12 @@ class Ref:
         sz = self.L.srt_ref_scene(idx, sp.ctypes.data, 488, C.byref(cnt), C.byref(sky), hdr.ctypes.data)
         assert sz == SPHERE_BYTES, sz
         return sp[:cnt.value].copy(), bool(sky.value), hdr
+
+    def set_scene(self, slot, spheres, sky, header):
+        spheres = np.ascontiguousarray(spheres)
+        header = np.ascontiguousarray(header, np.float32)
+        r = self.L.srt_ref_set_scene(slot, spheres.ctypes.data, len(spheres), int(sky), header.ctypes.data)
+        assert r == 0, r
 
     def render(self, scene, w, h, spp, simd=1, threads=0, flags=3, stream_base=0, tap_sample=0):
         rgba = np.zeros((h, w), np.uint32)

@@ -43,3 +43,21 @@ def test_stream_base(oracle, refs):
     r = refs["w8"].render(1, 64, 36, 2, simd=1, flags=3, stream_base=987654321012)
     o = oracle.render(sp, sky, 8, 1, cam, 64, 36, 0, 2, stream_base=987654321012)
     assert np.array_equal(o["accum"].view(np.uint32), r["accum"].view(np.uint32))
+
+
+def test_synthetic_scene_through_reference_code(oracle, refs):
+    """The reference's own RenderTile on the synthetic 1,024-sphere scene (injected through
+    srt_ref_set_scene) == the restatement, bit for bit (cameras from the host mirror)."""
+    import importlib
+    srt = importlib.import_module("simd-ray-tracer_b200")
+    sp, sky, hdr = srt.host_scene(srt.SCENE_SYNTH_1K)
+    cam = srt.host_camera(srt.SCENE_SYNTH_1K, 64, 36)
+    for lib, W, fma, simd in (("w8", 8, 1, 1), ("w4", 4, 0, 1), ("w4", 1, 0, 0)):
+        refs[lib].set_scene(1, sp, sky, hdr)
+        r = refs[lib].render(1, 64, 36, 2, simd=simd, flags=3)
+        o = oracle.render(sp, sky, W, fma, cam, 64, 36, 0, 2)
+        for k in ("accum", "rgba", "prim", "t"):
+            assert np.array_equal(o[k].view(np.uint32), r[k].view(np.uint32)), (lib, k)
+        assert o["rays"] == r["rays"]
+        b_sp, b_sky, b_hdr = oracle.scene(1)
+        refs[lib].set_scene(1, b_sp, b_sky, b_hdr)      # restore the built-in scene for later tests
