@@ -183,8 +183,7 @@ def run_gpu_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     scene_idx, W, H, SPP, desc = WORKLOADS[args.workload]
-    if SPP % n_gpus:
-        raise SystemExit(f"spp {SPP} not divisible by {n_gpus} GPUs")
+    shard = srt.sharding.plan(rank, n_gpus, SPP)
     spheres, sky, hdr = srt.host_scene(scene_idx)
     camera = srt.host_camera(scene_idx, W, H)
     n_pad = (len(spheres) + 7) // 8 * 8
@@ -216,9 +215,9 @@ def run_gpu_arm(args):
             b.render(camera, 0, SPP, stride=1, mode=srt.ACCUM_MEAN)
             ms, rays = b.wait()
         else:
-            b.render(camera, rank, SPP // n_gpus, stride=n_gpus, mode=srt.ACCUM_SUM)
+            b.render(camera, shard["first"], shard["count"], stride=shard["stride"], mode=srt.ACCUM_SUM)
             with torch.cuda.stream(ext_stream):
-                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+                srt.sharding.reduce_sum(dist, accum, dst=0)
             if rank == 0:
                 b.resolve_sum(SPP)
             ms, rays = b.wait()
@@ -270,9 +269,9 @@ def run_gpu_arm(args):
         if n_gpus == 1:
             b.render(cam_host, 0, SPP, stride=1, mode=srt.ACCUM_MEAN)   # H2D: camera (kernel params)
         else:
-            b.render(cam_host, rank, SPP // n_gpus, stride=n_gpus, mode=srt.ACCUM_SUM)
+            b.render(cam_host, shard["first"], shard["count"], stride=shard["stride"], mode=srt.ACCUM_SUM)
             with torch.cuda.stream(ext_stream):
-                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+                srt.sharding.reduce_sum(dist, accum, dst=0)
             if rank == 0:
                 b.resolve_sum(SPP)
         _, rays = b.wait()

@@ -277,6 +277,8 @@ typedef struct {
     int use_sky, lane_width, fma_dot;
     const orc_camera *cam;
     uint32_t width, height, first_sample, n_samples, tap_sample;
+    uint32_t sample_stride;     /* 0/1: contiguous running mean; >1 with sum_mode: sharded sum */
+    int sum_mode;               /* 1: accum += radiance (multi-GPU shard), no mean, no pack */
     uint64_t stream_base;
     float *accum;
     uint32_t *rgba, *tap_prim;
@@ -464,6 +466,18 @@ static void *orc_worker(void *arg) {
             const uint64_t pix = (uint64_t)y * W + x;
             float *acc = J->accum + pix * 4;
             float prev[4] = { acc[0], acc[1], acc[2], acc[3] };
+            if (J->sum_mode) {
+                /* sample-sharded partial sum: plain f32 adds in sample order */
+                const uint32_t stride = J->sample_stride ? J->sample_stride : 1;
+                for (uint32_t i = 0; i < J->n_samples; ++i) {
+                    const uint32_t k = J->first_sample + i * stride;
+                    uint64_t rng = orc_stream_seed(J->stream_base + (uint64_t)k * W * H + pix);
+                    v3 c = trace_path(J, x, y, &rng, &rays, 0, 0);
+                    prev[0] = prev[0] + c.x; prev[1] = prev[1] + c.y; prev[2] = prev[2] + c.z;
+                }
+                acc[0] = prev[0]; acc[1] = prev[1]; acc[2] = prev[2]; acc[3] = 1.0f;
+                continue;
+            }
             if (J->first_sample == 0) { prev[0] = prev[1] = prev[2] = prev[3] = 0.0f; }
             for (uint32_t k = J->first_sample; k < J->first_sample + J->n_samples; ++k) {
                 uint64_t rng = orc_stream_seed(J->stream_base + (uint64_t)k * W * H + pix);   /* P10 */
@@ -514,4 +528,40 @@ int orc_render(const orc_sphere *spheres, uint32_t n_spheres, int use_sky, int l
     pthread_mutex_destroy(&J.lock);
     if (rays) *rays = J.rays_total;
     return 0;
+}
+
+/* Sample-sharded partial SUM (the multi-GPU path): accum += radiance of samples
+ * first, first+stride, ... (n of them); then orc_resolve_sum() after the cross-rank sum. */
+int orc_render_sum(const orc_sphere *spheres, uint32_t n_spheres, int use_sky, int lane_width, int fma_dot,
+                   const orc_camera *camera, uint32_t width, uint32_t height,
+                   uint32_t first_sample, uint32_t n_samples, uint32_t sample_stride, uint64_t stream_base,
+                   float *accum, uint64_t *rays, int threads) {
+    if (!spheres || !camera || !accum || width == 0 || height == 0 || sample_stride == 0) return -1;
+    if (lane_width != 1 && lane_width != 4 && lane_width != 8) return -2;
+    orc_job J;
+    memset(&J, 0, sizeof(J));
+    J.spheres = spheres; J.n_spheres = n_spheres; J.use_sky = use_sky;
+    J.lane_width = lane_width; J.fma_dot = fma_dot; J.cam = camera;
+    J.width = width; J.height = height; J.first_sample = first_sample; J.n_samples = n_samples;
+    J.sample_stride = sample_stride; J.sum_mode = 1; J.stream_base = stream_base; J.accum = accum;
+    pthread_mutex_init(&J.lock, 0);
+    if (threads < 1) threads = 1;
+    if (threads > 256) threads = 256;
+    pthread_t tid[256];
+    for (int i = 1; i < threads; ++i) pthread_create(&tid[i], 0, orc_worker, &J);
+    orc_worker(&J);
+    for (int i = 1; i < threads; ++i) pthread_join(tid[i], 0);
+    pthread_mutex_destroy(&J.lock);
+    if (rays) *rays = J.rays_total;
+    return 0;
+}
+
+/* mean = sum * (1/N) (one f32 reciprocal, one multiply per channel), then A9. */
+void orc_resolve_sum(float *accum, uint32_t *rgba, uint32_t n_pixels, uint32_t total_samples) {
+    const float inv = 1.0f / (float)total_samples;
+    for (uint32_t i = 0; i < n_pixels; ++i) {
+        float *a = accum + (size_t)i * 4;
+        a[0] = a[0] * inv; a[1] = a[1] * inv; a[2] = a[2] * inv; a[3] = 1.0f;
+        if (rgba) rgba[i] = orc_pack(a);
+    }
 }

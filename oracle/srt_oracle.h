@@ -61,6 +61,14 @@ int orc_render(const orc_sphere *spheres, uint32_t n_spheres, int use_sky, int l
                float *accum, uint32_t *rgba, uint32_t *tap_prim, float *tap_t, uint32_t tap_sample,
                uint64_t *rays, int threads);
 
+/* Multi-GPU restatement (no counterpart in the reference): sharded f32 sum and
+ * its resolve. */
+int orc_render_sum(const orc_sphere *spheres, uint32_t n_spheres, int use_sky, int lane_width, int fma_dot,
+                   const orc_camera *camera, uint32_t width, uint32_t height,
+                   uint32_t first_sample, uint32_t n_samples, uint32_t sample_stride, uint64_t stream_base,
+                   float *accum, uint64_t *rays, int threads);
+void orc_resolve_sum(float *accum, uint32_t *rgba, uint32_t n_pixels, uint32_t total_samples);
+
 #ifdef __cplusplus
 }
 #endif

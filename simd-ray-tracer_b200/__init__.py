@@ -14,6 +14,7 @@ import os
 import numpy as np
 
 from . import build as _build
+from . import sharding  # noqa: F401
 
 PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = _build.LIB

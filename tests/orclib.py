@@ -58,6 +58,26 @@ class Oracle:
                                  C.c_uint32, C.c_uint32, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                  C.c_uint32, C.POINTER(C.c_uint64), C.c_int]
 
+    def render_sum(self, spheres, sky, lane_width, fma, cam, w, h, first, n, stride, accum=None, stream_base=0, threads=0):
+        spheres = np.ascontiguousarray(spheres)
+        if accum is None:
+            accum = np.zeros((h, w, 4), np.float32)
+        rays = C.c_uint64()
+        self.L.orc_render_sum.argtypes = [C.c_void_p, C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32,
+                                          C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_void_p, C.POINTER(C.c_uint64), C.c_int]
+        r = self.L.orc_render_sum(spheres.ctypes.data, len(spheres), int(sky), lane_width, int(fma), cam.ctypes.data, w, h,
+                                  first, n, stride, stream_base, accum.ctypes.data, C.byref(rays), threads or (os.cpu_count() or 1))
+        assert r == 0, r
+        return accum, rays.value
+
+    def resolve_sum(self, accum, total):
+        h, w = accum.shape[:2]
+        rgba = np.zeros((h, w), np.uint32)
+        self.L.orc_resolve_sum.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        self.L.orc_resolve_sum.restype = None
+        self.L.orc_resolve_sum(accum.ctypes.data, rgba.ctypes.data, h * w, total)
+        return rgba
+
     def scene(self, idx):
         sp = np.zeros(488, sphere_dtype)
         sky = C.c_int()
