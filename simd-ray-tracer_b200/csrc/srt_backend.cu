@@ -7,6 +7,7 @@
 #include "../../include/srt_backend.h"
 #include "srt_device.cuh"
 #include "srt_packed.cuh"
+#include "srt_pairs.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -204,6 +205,227 @@ render_paths(const __grid_constant__ KernelParams P) {
     if (lane == 0 && rays) atomicAdd(P.rays, rays);
 }
 
+// ------------------------------------------------------------------------------------------
+// render_pairs: the same pipeline A1..A9 with TWO paths per thread (slot 0 / slot 1) packed
+// into the halves of Blackwell's f32x2 instructions (srt_pairs.cuh).  Used for scenes large
+// enough for the intersection loop to dominate (>= kPairsMinSpheres).
+//
+// Everything a path carries between bounces -- ray, attenuation, radiance, running mean, RNG
+// state, pixel, sample index -- is parked in shared memory (field-major, conflict-free), so
+// the registers of the hot loop hold nothing but the two packed rays and its temporaries, and
+// the regenerate / shade phases are plain run-time loops over the two slots.
+// ------------------------------------------------------------------------------------------
+enum : int { S_OX, S_OY, S_OZ, S_DX, S_DY, S_DZ, S_AX, S_AY, S_AZ, S_LX, S_LY, S_LZ, S_MX, S_MY, S_MZ,
+             S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_COUNT };
+constexpr uint32_t kFlagBounceMask = 7u, kFlagActive = 8u, kFlagDone = 16u;
+
+template <int W, bool FMA, int THREADS, int MINB>
+__global__ void __launch_bounds__(THREADS, MINB)
+render_pairs(const __grid_constant__ KernelParams P) {
+    extern __shared__ float4 s_spheres[];
+    float4 *const s_scan = s_spheres + P.n_pad;
+    float *const st = reinterpret_cast<float *>(s_scan + P.n_pad);
+    uint32_t *const su = reinterpret_cast<uint32_t *>(st);
+    const uint32_t tid = threadIdx.x;
+    const unsigned lane = tid & 31u;
+#define SRT_ST(f, r) st[(((f) * THREADS) + tid) * 2 + (r)]
+#define SRT_SU(f, r) su[(((f) * THREADS) + tid) * 2 + (r)]
+    for (uint32_t i = tid; i < P.n_pad; i += THREADS) { s_spheres[i] = P.spheres[i]; s_scan[i] = P.scan_table[i]; }
+    const uint64_t plane = (uint64_t)P.width * P.height;
+    const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        SRT_SU(S_PIX, r) = kInvalidPixel;
+        SRT_SU(S_K, r) = k_end;
+        SRT_SU(S_FLAGS, r) = 0u;
+        SRT_ST(S_OX, r) = kIdleOrigin; SRT_ST(S_OY, r) = kIdleOrigin; SRT_ST(S_OZ, r) = kIdleOrigin;
+        SRT_ST(S_DX, r) = 0.0f; SRT_ST(S_DY, r) = 0.0f; SRT_ST(S_DZ, r) = 0.0f;
+    }
+    __syncthreads();
+    unsigned long long rays = 0;
+
+    for (;;) {
+        // ---- regenerate: finish pixels, fetch new ones, start new paths ----------------------
+        bool all_done = true;
+#pragma unroll 1
+        for (int r = 0; r < 2; ++r) {
+            uint32_t flags = SRT_SU(S_FLAGS, r);
+            const bool idle = (flags & (kFlagActive | kFlagDone)) == 0u;
+            if (__any_sync(0xFFFFFFFFu, idle)) {
+                uint32_t pix = SRT_SU(S_PIX, r), k = SRT_SU(S_K, r), pxy = SRT_SU(S_PXY, r);
+                bool need = idle && (k == k_end);
+                if (need && pix != kInvalidPixel) {
+                    // A8 result + A9 tonemap/pack, main.cpp:484-492
+                    const float mx = SRT_ST(S_MX, r), my = SRT_ST(S_MY, r), mz = SRT_ST(S_MZ, r);
+                    P.accum[pix] = make_float4(mx, my, mz, 1.0f);
+                    if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mx, my, mz);
+                    pix = kInvalidPixel;
+                }
+                unsigned m = __ballot_sync(0xFFFFFFFFu, need);
+                while (m) {
+                    const unsigned leader = __ffs(m) - 1;
+                    unsigned base = 0;
+                    if (lane == leader) base = atomicAdd(P.work_counter, __popc(m));
+                    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                    if (need) {
+                        const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
+                        uint32_t px, py;
+                        if (item >= P.total_items) { flags |= kFlagDone; need = false; }
+                        else if (item_to_pixel(P, item, px, py)) {
+                            pix = py * P.width + px;
+                            pxy = px | (py << 16);
+                            k = P.first_sample;
+                            need = false;
+                            float4 prev = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1), zeroed arena
+                            if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) prev = P.accum[pix];
+                            SRT_ST(S_MX, r) = prev.x; SRT_ST(S_MY, r) = prev.y; SRT_ST(S_MZ, r) = prev.z;
+                        }
+                    }
+                    m = __ballot_sync(0xFFFFFFFFu, need);
+                }
+                if (idle && !(flags & kFlagDone)) {
+                    // A1 primary ray, main.cpp:375-385; stream contract: SURVEY 8c P10
+                    uint64_t rng = stream_seed(P.stream_base + (uint64_t)k * plane + pix);
+                    const uint32_t px = pxy & 0xFFFFu, py = pxy >> 16;
+                    const float jx = rand_float(rng, kInvU32Range1, -0.5f);
+                    const float jy = rand_float(rng, kInvU32Range1, -0.5f);
+                    const float film_x = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)px, jx), 2.0f), (float)P.width));
+                    const float film_y = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)py, jy), 2.0f), (float)P.height));
+                    const float ax = __fmul_rn(__fmul_rn(film_x, P.cam.film_w), 0.5f);
+                    const float ay = __fmul_rn(__fmul_rn(film_y, P.cam.film_h), 0.5f);
+                    const f3 cam_x = mk3(P.cam.x[0], P.cam.x[1], P.cam.x[2]);
+                    const f3 cam_y = mk3(P.cam.y[0], P.cam.y[1], P.cam.y[2]);
+                    const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
+                    const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
+                    const f3 o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+                    const f3 d = normalize3(sub3(film_p, o));
+                    SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
+                    SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
+                    SRT_ST(S_AX, r) = 1.0f; SRT_ST(S_AY, r) = 1.0f; SRT_ST(S_AZ, r) = 1.0f;
+                    SRT_ST(S_LX, r) = 0.0f; SRT_ST(S_LY, r) = 0.0f; SRT_ST(S_LZ, r) = 0.0f;
+                    SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
+                    flags = kFlagActive;                                           // bounce 0
+                } else if (idle) {
+                    // out of work: park the slot where no sphere can be a candidate
+                    SRT_ST(S_OX, r) = kIdleOrigin; SRT_ST(S_OY, r) = kIdleOrigin; SRT_ST(S_OZ, r) = kIdleOrigin;
+                    SRT_ST(S_DX, r) = 0.0f; SRT_ST(S_DY, r) = 0.0f; SRT_ST(S_DZ, r) = 0.0f;
+                }
+                SRT_SU(S_PIX, r) = pix; SRT_SU(S_K, r) = k; SRT_SU(S_PXY, r) = pxy; SRT_SU(S_FLAGS, r) = flags;
+            }
+            all_done = all_done && (flags & kFlagDone);
+        }
+        if (__all_sync(0xFFFFFFFFu, all_done)) break;
+
+        // ---- A3/A4 brute-force intersection over ALL spheres, both slots at once ------------
+        Hit h0, h1;
+        {
+            const pk2 *const ray = reinterpret_cast<const pk2 *>(st);
+            const pk2 ox = ray[S_OX * THREADS + tid], oy = ray[S_OY * THREADS + tid], oz = ray[S_OZ * THREADS + tid];
+            const pk2 dx = ray[S_DX * THREADS + tid], dy = ray[S_DY * THREADS + tid], dz = ray[S_DZ * THREADS + tid];
+            intersect_pair<W, FMA>(s_scan, s_spheres, P.n_pad, P.n_spheres, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, h0, h1);
+        }
+
+        // ---- shade / scatter, one slot after the other ---------------------------------------
+#pragma unroll 1
+        for (int r = 0; r < 2; ++r) {
+            uint32_t flags = SRT_SU(S_FLAGS, r);
+            if (!(flags & kFlagActive)) continue;
+            rays += 1;                                                        // main.cpp:390
+            const Hit h = r ? h1 : h0;
+            const uint32_t pix = SRT_SU(S_PIX, r);
+            uint32_t k = SRT_SU(S_K, r);
+            uint32_t bounce = flags & kFlagBounceMask;
+            f3 o = mk3(SRT_ST(S_OX, r), SRT_ST(S_OY, r), SRT_ST(S_OZ, r));
+            f3 d = mk3(SRT_ST(S_DX, r), SRT_ST(S_DY, r), SRT_ST(S_DZ, r));
+            f3 atten = mk3(SRT_ST(S_AX, r), SRT_ST(S_AY, r), SRT_ST(S_AZ, r));
+            f3 out = mk3(SRT_ST(S_LX, r), SRT_ST(S_LY, r), SRT_ST(S_LZ, r));
+            if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
+                P.tap_t[pix] = h.t;
+                P.tap_prim[pix] = h.prim;
+            }
+            bool path_end = false;
+            if (!h.hit) {
+                if (P.use_sky) {                                              // A5 main.cpp:433-440
+                    const float a = __fmul_rn(__fadd_rn(d.y, 1.0f), 0.5f);
+                    const float ia = __fsub_rn(1.0f, a);
+                    const f3 sky = add3(scale3(ia, mk3(1.0f, 1.0f, 1.0f)), scale3(a, mk3(0.5f, 0.7f, 1.0f)));
+                    out = add3(out, mul3(sky, atten));
+                }
+                path_end = true;
+            } else {
+                // ---- A6 shade + scatter, main.cpp:443-481 -------------------------------------
+                uint64_t rng = (uint64_t)SRT_SU(S_RNG_LO, r) | ((uint64_t)SRT_SU(S_RNG_HI, r) << 32);
+                const DevMaterial *M = &P.materials[h.prim];
+                const float4 cs = __ldg(&M->color_spec);
+                const float4 ei = __ldg(&M->emis_ior);
+                const float4 dv = __ldg(&M->derived);
+                out = add3(out, mul3(mk3(ei.x, ei.y, ei.z), atten));
+                atten = mul3(atten, mk3(cs.x, cs.y, cs.z));
+                // winner's HitNormal / NextRayOrigin, recomputed with the ops of main.cpp:423-429
+                const float4 s = s_spheres[h.prim];
+                const f3 sc = sub3(mk3(s.x, s.y, s.z), o);
+                const f3 ip = scale3(h.t, d);
+                o = add3(o, ip);
+                f3 n = normalize3(sub3(ip, sc));
+                const f3 pure = sub3(d, scale3(__fmul_rn(2.0f, dot3(d, n)), n));   // :453
+                if (h.inside) n = neg3(n);
+                if (ei.w == 0.0f) {
+                    const float rx = rand_float(rng, kInvU32Range2, -1.0f);
+                    const float ry = rand_float(rng, kInvU32Range2, -1.0f);
+                    const float rz = rand_float(rng, kInvU32Range2, -1.0f);
+                    const f3 rr = normalize3(mk3(rx, ry, rz));                     // :461
+                    const f3 rb = add3(n, rr);
+                    d = normalize3(add3(scale3(dv.x, rb), scale3(cs.w, pure)));    // :463-464
+                } else {
+                    const float eta = h.inside ? ei.w : dv.y;                      // :466
+                    const float cd = dot3(neg3(d), n);
+                    const float c = (cd < 1.0f) ? cd : 1.0f;                       // _mm_min_ss :468
+                    const float cc = __fmul_rn(c, c);
+                    const float sn = __fsqrt_rn(__double2float_rn(__dsub_rn(1.0, (double)cc)));   // :469
+                    const bool cant = __fmul_rn(eta, sn) > 1.0f;                   // :471
+                    const f3 perp = scale3(eta, add3(d, scale3(c, n)));            // :472
+                    const float kk = -__fsqrt_rn(fabsf(__fsub_rn(1.0f, dot3(perp, perp))));   // :473
+                    const f3 refr = normalize3(add3(perp, scale3(kk, n)));         // :474
+                    bool reflect = cant;                                            // :476 (|| short-circuit)
+                    if (!cant) reflect = reflectance(c, eta) > rand_float(rng, kInvU32Range1, 0.0f);
+                    d = (reflect && !h.inside) ? pure : refr;
+                }
+                bounce += 1;
+                path_end = (bounce == kMaxBounce);
+                SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
+                SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
+                SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
+                SRT_ST(S_AX, r) = atten.x; SRT_ST(S_AY, r) = atten.y; SRT_ST(S_AZ, r) = atten.z;
+            }
+            if (path_end) {
+                f3 mean = mk3(SRT_ST(S_MX, r), SRT_ST(S_MY, r), SRT_ST(S_MZ, r));
+                if (P.accum_mode == SRT_ACCUM_MEAN) {
+                    // A8 running mean, main.cpp:484-489 (k == PreviousRayCount)
+                    const float total = (float)(k + 1u);
+                    const float wa = __fdiv_rn(1.0f, total);
+                    const float wb = __fdiv_rn((float)k, total);
+                    mean = add3(scale3(wa, out), scale3(wb, mean));
+                } else {
+                    mean = add3(mean, out);
+                }
+                SRT_ST(S_MX, r) = mean.x; SRT_ST(S_MY, r) = mean.y; SRT_ST(S_MZ, r) = mean.z;
+                SRT_SU(S_K, r) = k + P.sample_stride;
+                flags = 0u;                                                   // idle; regenerated next pass
+            } else {
+                SRT_ST(S_LX, r) = out.x; SRT_ST(S_LY, r) = out.y; SRT_ST(S_LZ, r) = out.z;
+                flags = kFlagActive | bounce;
+            }
+            SRT_SU(S_FLAGS, r) = flags;
+        }
+    }
+#undef SRT_ST
+#undef SRT_SU
+
+    // rays: one atomic per warp
+    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
+    if (lane == 0 && rays) atomicAdd(P.rays, rays);
+}
+
 // mean = sum * (1/N); tonemap + pack.  HBM-bound: 16 B read + 16 B + 4 B written per pixel.
 __global__ void resolve_sum_kernel(float4 *accum, uint32_t *rgba, uint32_t n_pixels, float inv_n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -230,8 +452,10 @@ struct srt_backend {
     // scene
     float4 *d_spheres = nullptr;         // {cx,cy,cz,r2} per sphere (scalar-issue kernels)
     float4 *d_spheres2 = nullptr;        // sphere-pair layout (packed f32x2 kernels)
+    float4 *d_scan = nullptr;            // filter table of the ray-pair kernel {cx,cy,cz,-kappa}
     DevMaterial *d_materials = nullptr;
-    int variant = 0;                     // 0: packed f32x2 loop; 1: scalar-issue loop (diagnostic)
+    int variant = 0;                     // 0: auto; 1: scalar-issue loop; 2..6: sphere-pair tuning; 7: force sphere-pair;
+                                         // 8: force ray-pair kernel (diagnostics, SRT_KERNEL_VARIANT)
     uint32_t regen_threshold = 1;
     uint32_t n_spheres = 0, n_pad = 0;
     srt_scene_options opt = {0, 8, 1, 0};
@@ -284,6 +508,20 @@ static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed, int 
     return o.fma_dot ? render_paths<8, true, false> : render_paths<8, false, false>;
 }
 
+// Ray-pair kernel (srt_pairs.cuh): used when the scene is large enough for the intersection
+// loop to dominate and small enough for both sphere tables to stay resident in shared memory.
+constexpr int kPairThreads = 256;
+constexpr int kPairMinBlocks = 2;
+constexpr uint32_t kPairsMinSpheres = 64;
+static render_kernel_t pick_pairs_kernel(const srt_scene_options &o) {
+    if (o.lane_width == 1) return render_pairs<1, false, kPairThreads, kPairMinBlocks>;
+    if (o.lane_width == 4) return o.fma_dot ? render_pairs<4, true, kPairThreads, kPairMinBlocks> : render_pairs<4, false, kPairThreads, kPairMinBlocks>;
+    return o.fma_dot ? render_pairs<8, true, kPairThreads, kPairMinBlocks> : render_pairs<8, false, kPairThreads, kPairMinBlocks>;
+}
+static size_t pairs_smem_bytes(uint32_t n_pad) {
+    return (size_t)n_pad * 2 * sizeof(float4) + (size_t)S_COUNT * 2 * kPairThreads * sizeof(float);
+}
+
 extern "C" {
 
 const char *srt_last_error(const srt_backend *b) { return b ? b->err.c_str() : g_create_error.c_str(); }
@@ -322,7 +560,7 @@ void srt_destroy(srt_backend *b) {
     if (!b) return;
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
-    cudaFree(b->d_spheres); cudaFree(b->d_spheres2); cudaFree(b->d_materials);
+    cudaFree(b->d_spheres); cudaFree(b->d_spheres2); cudaFree(b->d_scan); cudaFree(b->d_materials);
     cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
     cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
     cudaFree(b->d_counters);
@@ -374,10 +612,23 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
         sph2[2 * p] = make_float4(e.x, o.x, e.y, o.y);
         sph2[2 * p + 1] = make_float4(e.z, o.z, e.w, o.w);
     }
+    // Filter table of the ray-pair kernel (srt_pairs.cuh): -kappa_i = R_i - |C_i|^2
+    // with R_i = r2 (1 + 128u) + 128u |C|^2, evaluated in double.  Padding can never be a candidate.
+    std::vector<float4> scan(n_pad, make_float4(0.f, 0.f, 0.f, -1.0e30f));
+    for (uint32_t i = 0; i < n_spheres; ++i) {
+        const double u = 5.9604644775390625e-08;
+        const double cx = sph[i].x, cy = sph[i].y, cz = sph[i].z, r2 = sph[i].w;
+        const double c2 = cx * cx + cy * cy + cz * cz;
+        const double R = r2 * (1.0 + 128.0 * u) + 128.0 * u * c2 + 1.0e-30;
+        scan[i] = make_float4(sph[i].x, sph[i].y, sph[i].z, (float)(R - c2));
+    }
     cudaFree(b->d_spheres); b->d_spheres = nullptr;
+    cudaFree(b->d_scan); b->d_scan = nullptr;
     cudaFree(b->d_spheres2); b->d_spheres2 = nullptr;
     cudaFree(b->d_materials); b->d_materials = nullptr;
     SRT_CUDA(b, cudaMalloc(&b->d_spheres, sph.size() * sizeof(float4)));
+    SRT_CUDA(b, cudaMalloc(&b->d_scan, scan.size() * sizeof(float4)));
+    SRT_CUDA(b, cudaMemcpy(b->d_scan, scan.data(), scan.size() * sizeof(float4), cudaMemcpyHostToDevice));
     SRT_CUDA(b, cudaMalloc(&b->d_spheres2, sph2.size() * sizeof(float4)));
     SRT_CUDA(b, cudaMemcpy(b->d_spheres2, sph2.data(), sph2.size() * sizeof(float4), cudaMemcpyHostToDevice));
     SRT_CUDA(b, cudaMalloc(&b->d_materials, mats.size() * sizeof(DevMaterial)));
@@ -458,8 +709,12 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
 
     KernelParams P;
     memset(&P, 0, sizeof(P));
-    const bool packed = (b->variant != 1) && b->opt.lane_width != 1;
+    const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad) <= b->max_smem_optin;
+    const bool pairs = pairs_fit && (b->variant == 8 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
+    if (b->variant == 8 && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
+    const bool packed = !pairs && (b->variant != 1) && b->opt.lane_width != 1;
     P.spheres = packed ? b->d_spheres2 : b->d_spheres;
+    P.scan_table = b->d_scan;
     P.regen_threshold = b->regen_threshold;
     P.neg_one = -1.0f;
     P.one = 1.0f;
@@ -499,19 +754,21 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     P.rays = (unsigned long long *)b->d_counters;
     P.work_counter = (unsigned int *)(b->d_counters + 8);
 
-    render_kernel_t kernel = pick_kernel(b->opt, packed, b->variant);
-    const size_t smem = (size_t)b->n_pad * sizeof(float4);
+    render_kernel_t kernel = pairs ? pick_pairs_kernel(b->opt) : pick_kernel(b->opt, packed, b->variant);
+    const int threads = pairs ? kPairThreads : kBlockThreads;
+    const size_t smem = pairs ? pairs_smem_bytes(b->n_pad) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kBlockThreads, smem));
+    SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
     if (per_sm < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
     uint32_t grid = (uint32_t)(b->sm_count * per_sm);                 // persistent: one resident wave
-    const uint32_t max_useful = (P.total_items + kBlockThreads - 1) / kBlockThreads;
+    const uint32_t paths_per_block = (uint32_t)threads * (pairs ? 2u : 1u);
+    const uint32_t max_useful = (P.total_items + paths_per_block - 1) / paths_per_block;
     if (grid > max_useful) grid = max_useful;
 
     SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 16, b->stream));
     SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
-    kernel<<<grid, kBlockThreads, smem, b->stream>>>(P);
+    kernel<<<grid, threads, smem, b->stream>>>(P);
     SRT_CUDA(b, cudaGetLastError());
     SRT_CUDA(b, cudaEventRecord(b->ev_stop, b->stream));
     SRT_CUDA(b, cudaMemcpyAsync(b->h_rays, b->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, b->stream));

@@ -1,0 +1,211 @@
+// srt_pairs.cuh -- brute-force intersection for a PAIR OF RAYS per thread (sm_100a):
+// a conservative fused-arithmetic FILTER over all spheres, then the reference's exact
+// arithmetic on the few survivors.
+//
+// Why.  ncu on the sphere-pair kernel (profiles/r1b_ncu_full_render_paths_v1.txt) plus the
+// microbenchmarks in scripts/microbench show that on B200 a packed FFMA2/FMUL2/FADD2 holds the
+// scheduler's issue port for 2 cycles: the 15 separately rounded instructions of
+// main.cpp:401-409 cost 30 issue cycles per sphere per warp however they are scheduled, and
+// every other instruction (LDS, compare, hit bookkeeping) adds to that.  The only way below
+// that floor is to NOT execute the reference's instruction sequence for spheres the ray
+// misses -- while still testing every sphere against every ray and still producing the
+// reference's bits.
+//
+// Scan (all spheres, 7 packed FMAs + 2 compares + 1 mask update per sphere per ray pair).
+//   With w = C - O and tau = w.D the reference decides a hit on d2 = |w - D tau|^2
+//   = |w|^2 - tau^2 (2 - |D|^2).  The scan evaluates the same quantity from per-ray and
+//   per-sphere constants,
+//       z = tt^2 + (2 C.O - kappa_i),   tt = C.D' - O.D',   D' = D sqrt(2 - |D|^2),
+//       kappa_i = |C_i|^2 - R_i,        candidate  <=>  z > oo',
+//   where R_i = r2_i (1 + 128u) + 128u |C_i|^2 is the sphere's squared radius inflated on the
+//   host (in double) and oo' = |O|^2 (1 - 160u) is deflated per ray, u = 2^-24.  DESIGN.md
+//   section 5.3 bounds every rounding of both evaluation orders and shows that the
+//   reference's `d2 < r2` (SIMD) or `!(d2 > r2)` (scalar) implies z > oo' with a 1.5x safety
+//   factor: the scan never loses a hit, it only admits a few near misses.
+//   `srt_filter_audit` (tests/test_gpu_filter.py) checks that superset property exhaustively
+//   on the GPU for every (ray, sphere) pair of whole renders.
+// Select (candidates only).  The reference's own instruction sequence, packed over the two
+//   rays, in increasing sphere index: t and d2 have the reference's bits, so hit/miss,
+//   closest-hit choice, tie-break and inside flag are bit-identical.
+//
+// Lane semantics.  Sphere s is lane s % W of group s / W; strict `<` per lane; HorizontalMin,
+// first lane holding it (main.cpp:419-455).  That reduces to: smallest t wins; equal t ->
+// lower lane; equal lane -> earlier group.  The sticky InsideSphere bit (main.cpp:425) of the
+// winning lane is the OR of `test` over that lane's accepted updates; it can differ from the
+// winner's own `test` only if an earlier candidate of the same lane had test == true, which
+// is detected (`test_lanes`) and resolved by the literal per-lane emulation (replay_inside).
+#pragma once
+#include "srt_device.cuh"
+#include "srt_packed.cuh"
+
+namespace srt {
+
+constexpr int kPairsMaxSpheres = 8192;                  // resident-scene limit of the pair kernel
+constexpr int kPairsMaxWords = kPairsMaxSpheres / 32;   // candidate bitmap words per thread
+constexpr float kIdleOrigin = 3.0e18f;                  // parked slot: no sphere is ever a candidate
+constexpr float kFilterU = 5.9604644775390625e-08f;     // u = 2^-24
+
+// Running closest-hit state of one ray while candidates are replayed.
+struct Best {
+    float t;               // MinT after HorizontalMin
+    uint32_t idx;          // sphere index of the winner
+    uint32_t test;         // winner's own `t - x < eps` flag (main.cpp:416)
+    uint32_t test_lanes;   // lanes in which a valid test == true candidate was seen
+};
+__device__ __forceinline__ Best best_init() { Best b; b.t = kMax; b.idx = 0; b.test = 0; b.test_lanes = 0; return b; }
+
+// main.cpp:413-427 for one candidate of one ray (the hit test was done by the caller).
+template <int W>
+__device__ __forceinline__ void best_update(Best &B, float t, float d2, float r2, uint32_t idx) {
+    const float x = __fsqrt_rn(__fsub_rn(r2, d2));                       // :413
+    float it = __fsub_rn(t, x);                                          // :415
+    const bool test = it < kEps;                                         // :416
+    if (test) it = __fadd_rn(t, x);                                      // :417
+    if (W == 1) {                                                        // RenderTileScalar :568-576
+        if (!(it > B.t) && !(it < kEps)) { B.t = it; B.idx = idx; B.test = test; }
+    } else if (it > kEps) {                                              // :419-421
+        const uint32_t lane = idx & (uint32_t)(W - 1);
+        if (test) B.test_lanes |= 1u << lane;
+        if (it < B.t || (it == B.t && lane < (B.idx & (uint32_t)(W - 1)))) { B.t = it; B.idx = idx; B.test = test; }
+    }
+}
+
+// Literal per-lane emulation for the ambiguous sticky-inside case; out of line on purpose
+// (rare, and its MinT[W]/group[W] registers must not count against the hot kernel).
+template <int W, bool FMA>
+__device__ __noinline__ uint32_t replay_inside(const float4 *sph, uint32_t n_pad, float ox, float oy, float oz, float dx, float dy, float dz) {
+    const Hit h = intersect_lanes<(W == 1 ? 4 : W), FMA>(sph, n_pad, mk3(ox, oy, oz), mk3(dx, dy, dz));
+    return h.inside ? 1u : 0u;
+}
+
+// Per-ray constants of the filter (one ray; a few dozen instructions per pass).
+struct FilterRay {
+    float p2ox, p2oy, p2oz;   // 2 O (exact)
+    float dx, dy, dz;         // D' = D sqrt(2 - |D|^2)
+    float od;                 // -(O . D')
+    float oo;                 // |O|^2 deflated by 160u; -inf if D is not (nearly) unit or zero
+};
+__device__ __forceinline__ FilterRay filter_ray(float ox, float oy, float oz, float dx, float dy, float dz) {
+    FilterRay f;
+    f.p2ox = __fmul_rn(2.0f, ox); f.p2oy = __fmul_rn(2.0f, oy); f.p2oz = __fmul_rn(2.0f, oz);
+    const float dd = __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx)));
+    const float g = __fsqrt_rn(__fsub_rn(2.0f, dd));
+    f.dx = __fmul_rn(dx, g); f.dy = __fmul_rn(dy, g); f.dz = __fmul_rn(dz, g);
+    f.od = -__fmaf_rn(oz, f.dz, __fmaf_rn(oy, f.dy, __fmul_rn(ox, f.dx)));
+    const float oo = __fmaf_rn(oz, oz, __fmaf_rn(oy, oy, __fmul_rn(ox, ox)));
+    f.oo = __fmul_rn(oo, 1.0f - 160.0f * kFilterU);
+    if (!(dd < 1.5f)) {   // exotic direction (never produced by the path tracer): every sphere is a candidate
+        f.dx = 0.0f; f.dy = 0.0f; f.dz = 0.0f; f.od = 0.0f;
+        f.oo = -__int_as_float(0x7f800000);
+    }
+    return f;
+}
+
+// mask |= bit  iff  za > ooa || zb > oob : FSETP, FSETP.OR, predicated LOP3.
+__device__ __forceinline__ void filter_mark(uint32_t &mask, float za, float ooa, float zb, float oob, uint32_t bit) {
+    asm("{\n\t.reg .pred p;\n\tsetp.gt.f32 p, %1, %2;\n\tsetp.gt.or.f32 p, %3, %4, p;\n\t@p or.b32 %0, %0, %5;\n\t}"
+        : "+r"(mask) : "f"(za), "f"(ooa), "f"(zb), "f"(oob), "r"(bit));
+}
+
+// One sphere of the scan: {cx, cy, cz, -kappa} against the packed ray pair.
+__device__ __forceinline__ void filter_sphere(uint32_t &mask, uint32_t bit, const float4 s, pk2 p2ox, pk2 p2oy, pk2 p2oz,
+                                              pk2 dx, pk2 dy, pk2 dz, pk2 od, float ooa, float oob) {
+    const pk2 cx = pk_make(s.x, s.x), cy = pk_make(s.y, s.y), cz = pk_make(s.z, s.z);
+    const pk2 nq = pk_fma(cx, p2ox, pk_fma(cy, p2oy, pk_fma(cz, p2oz, pk_make(s.w, s.w))));   // 2 C.O - kappa
+    const pk2 tt = pk_fma(cx, dx, pk_fma(cy, dy, pk_fma(cz, dz, od)));                        // (C - O).D'
+    const pk2 z = pk_fma(tt, tt, nq);
+    float za, zb;
+    pk_split(z, za, zb);
+    filter_mark(mask, za, ooa, zb, oob, bit);
+}
+
+// Scan + select for the two rays of a thread.
+//   scan : shared memory, n_pad x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
+//   sph  : shared memory, n_pad x {cx, cy, cz, r2}     (the reference's operands, padding zero)
+//   o*/d*: packed {slot0, slot1} origins and directions
+// The candidate bitmap (bit 31 - j of word c = sphere 32 c + j) lives in LOCAL memory on
+// purpose: ptxas cannot prove that a shared-memory store does not alias the sphere tables and
+// would serialise the next LDS.128 behind it.  One STL per 32 spheres.
+template <int W, bool FMA>
+__device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float4 *__restrict__ sph,
+                                               uint32_t n_pad, uint32_t n_real,
+                                               pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
+                                               float neg_one_f, float one_f, Hit &h0, Hit &h1) {
+    uint32_t bitmap[kPairsMaxWords];
+    const uint32_t n_words = (n_pad + 31u) >> 5;
+    {
+        // ---- scan: every sphere, both rays, fused arithmetic, branch-free --------------------
+        float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
+        pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
+        pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
+        const FilterRay fa = filter_ray(oxa, oya, oza, dxa, dya, dza), fb = filter_ray(oxb, oyb, ozb, dxb, dyb, dzb);
+        const pk2 p2ox = pk_make(fa.p2ox, fb.p2ox), p2oy = pk_make(fa.p2oy, fb.p2oy), p2oz = pk_make(fa.p2oz, fb.p2oz);
+        const pk2 fdx = pk_make(fa.dx, fb.dx), fdy = pk_make(fa.dy, fb.dy), fdz = pk_make(fa.dz, fb.dz);
+        const pk2 od = pk_make(fa.od, fb.od);
+        const uint32_t full = n_pad >> 5;
+#pragma unroll 1
+        for (uint32_t c = 0; c < full; ++c) {
+            uint32_t mask = 0;
+            const float4 *blk = scan + (c << 5);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) filter_sphere(mask, 0x80000000u >> j, blk[j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
+            bitmap[c] = mask;
+        }
+        if (n_pad & 31u) {                       // tail: 1..3 blocks of 8
+            uint32_t mask = 0;
+#pragma unroll 1
+            for (uint32_t base = full << 5; base < n_pad; base += 8) {
+                const uint32_t bit0 = 0x80000000u >> (base & 31u);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) filter_sphere(mask, bit0 >> j, scan[base + j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
+            }
+            bitmap[full] = mask;
+        }
+    }
+    // ---- select: the reference's arithmetic on the candidates, in index order ----------------
+    const pk2 neg_one = pk_make(neg_one_f, neg_one_f), one = pk_make(one_f, one_f);
+    Best b0 = best_init(), b1 = best_init();
+    for (uint32_t c = 0; c < n_words; ++c) {
+        uint32_t m = bitmap[c];
+        while (m) {
+            const uint32_t j = (uint32_t)__clz((int)m);
+            m &= ~(0x80000000u >> j);
+            const uint32_t idx = (c << 5) + j;
+            const float4 s = sph[idx];
+            const pk2 scx = pk_sub(pk_make(s.x, s.x), ox);                         // main.cpp:401
+            const pk2 scy = pk_sub(pk_make(s.y, s.y), oy);
+            const pk2 scz = pk_sub(pk_make(s.z, s.z), oz);
+            const pk2 t2 = pk_dot<FMA>(scx, scy, scz, dx, dy, dz, one);            // :402
+            const pk2 vx = pk_fma(pk_mul(dx, t2), neg_one, scx);                   // :403,407
+            const pk2 vy = pk_fma(pk_mul(dy, t2), neg_one, scy);
+            const pk2 vz = pk_fma(pk_mul(dz, t2), neg_one, scz);
+            const pk2 dd = pk_dot<FMA>(vx, vy, vz, vx, vy, vz, one);
+            float d2a, d2b, ta, tb;
+            pk_split(dd, d2a, d2b);
+            pk_split(t2, ta, tb);
+            if (W == 1) {
+                // `d2 > r2 -> continue` (:557) lets NaN through, so padding is excluded by index.
+                if (!(d2a > s.w) && idx < n_real) best_update<W>(b0, ta, d2a, s.w, idx);
+                if (!(d2b > s.w) && idx < n_real) best_update<W>(b1, tb, d2b, s.w, idx);
+            } else {
+                if (d2a < s.w) best_update<W>(b0, ta, d2a, s.w, idx);              // :409
+                if (d2b < s.w) best_update<W>(b1, tb, d2b, s.w, idx);
+            }
+        }
+    }
+    h0.t = b0.t; h0.hit = !(b0.t == kMax); h0.prim = h0.hit ? b0.idx : 0xFFFFFFFFu; h0.inside = b0.test != 0;
+    h1.t = b1.t; h1.hit = !(b1.t == kMax); h1.prim = h1.hit ? b1.idx : 0xFFFFFFFFu; h1.inside = b1.test != 0;
+    if (W != 1) {
+        const bool amb0 = h0.hit && !b0.test && ((b0.test_lanes >> (b0.idx & (uint32_t)(W - 1))) & 1u);
+        const bool amb1 = h1.hit && !b1.test && ((b1.test_lanes >> (b1.idx & (uint32_t)(W - 1))) & 1u);
+        if (amb0 || amb1) {
+            float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
+            pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
+            pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
+            if (amb0) h0.inside = replay_inside<W, FMA>(sph, n_pad, oxa, oya, oza, dxa, dya, dza) != 0;
+            if (amb1) h1.inside = replay_inside<W, FMA>(sph, n_pad, oxb, oyb, ozb, dxb, dyb, dzb) != 0;
+        }
+    }
+}
+
+} // namespace srt
