@@ -36,6 +36,7 @@ EXPORTS = [
     "srt_reset_accumulation", "srt_bind_device_buffers", "srt_render", "srt_poll", "srt_wait",
     "srt_resolve_sum", "srt_read_rgba8", "srt_read_accum", "srt_read_primary",
     "srt_accum_device_ptr", "srt_rgba_device_ptr", "srt_cuda_stream", "srt_device_info",
+    "srt_filter_audit",
 ]
 
 
@@ -78,6 +79,7 @@ def load_library():
     L.srt_poll.argtypes = [vp]
     L.srt_wait.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     L.srt_resolve_sum.argtypes = [vp, C.c_uint32]
+    L.srt_filter_audit.argtypes = [vp, vp, C.POINTER(RenderArgs), C.POINTER(C.c_uint64)]
     L.srt_read_rgba8.argtypes = [vp, vp]
     L.srt_read_accum.argtypes = [vp, vp]
     L.srt_read_primary.argtypes = [vp, vp, vp]
@@ -144,6 +146,14 @@ class Backend:
         ms, rays = C.c_double(), C.c_uint64()
         self._check(self.L.srt_wait(self.h, C.byref(ms), C.byref(rays)))
         return ms.value, rays.value
+
+    def filter_audit(self, camera, first_sample=0, n_samples=1, stream_base=0):
+        """Soundness audit of the ray-pair kernel's sphere filter: dict(tests, hits, candidates, violations)."""
+        cam = np.ascontiguousarray(camera)
+        args = RenderArgs(first_sample, n_samples, 1, ACCUM_MEAN, stream_base, 0, 0)
+        counts = (C.c_uint64 * 4)()
+        self._check(self.L.srt_filter_audit(self.h, cam.ctypes.data, C.byref(args), counts))
+        return dict(tests=counts[0], hits=counts[1], candidates=counts[2], violations=counts[3])
 
     def resolve_sum(self, total_samples):
         self._check(self.L.srt_resolve_sum(self.h, total_samples))

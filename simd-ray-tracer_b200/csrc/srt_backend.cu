@@ -8,6 +8,7 @@
 #include "srt_device.cuh"
 #include "srt_packed.cuh"
 #include "srt_pairs.cuh"
+#include "srt_path.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -18,30 +19,19 @@
 namespace srt {
 
 constexpr int kBlockThreads = 256;
-constexpr uint32_t kInvalidPixel = 0xFFFFFFFFu;
-
-// Work item i -> pixel: 8x4 pixel blocks, row-major over blocks, so that a fresh warp
-// covers a compact screen patch (coherent primary rays: the rare hit branch and the
-// material branch diverge less).  Returns false for items outside the image.
-__device__ __forceinline__ bool item_to_pixel(const KernelParams &P, uint32_t item, uint32_t &px, uint32_t &py) {
-    const uint32_t blk = item >> 5, in = item & 31u;
-    const uint32_t bx = blk % P.blocks_x, by = blk / P.blocks_x;
-    px = bx * 8u + (in & 7u);
-    py = by * 4u + (in >> 3);
-    return px < P.width && py < P.height;
-}
 
 // ------------------------------------------------------------------------------------------
-// render_paths: the whole per-pixel pipeline A1..A9.
+// render_paths: the whole per-pixel pipeline A1..A9, ONE path per
+// thread.  Used for small scenes (shading-bound) and as the diagnostic baseline.
 //
-// Persistent CTAs, one path per thread, PATH REGENERATION: a thread whose path ended
-// (miss or 5th bounce) immediately starts the next sample of its pixel, or pulls the next
-// pixel from a global counter (warp-aggregated atomic), so all 32 lanes of a warp enter
-// the brute-force intersection loop together no matter how many bounces each path takes.
-// A thread owns a pixel for all n_samples of the launch: the running mean lives in
-// registers and the framebuffers are touched once per pixel per launch (16 B read when
-// first_sample > 0, 16 B + 4 B written).  The scene SoA sits in shared memory and is read
-// with warp-uniform LDS.128 broadcasts.
+// Persistent CTAs, PATH REGENERATION: a thread whose path ended (miss or 5th bounce)
+// immediately starts the next sample of its pixel, or pulls the next pixel from a global
+// counter (warp-aggregated atomic), so all 32 lanes of a warp enter the brute-force
+// intersection loop together no matter how many bounces each path takes.  A thread owns a
+// pixel for all n_samples of the launch: the running mean lives in registers and the
+// framebuffers are touched once per pixel per launch (16 B read when first_sample > 0,
+// 16 B + 4 B written).  The scene SoA sits in shared memory and is read with warp-uniform
+// LDS.128 broadcasts.
 // ------------------------------------------------------------------------------------------
 template <int W, bool FMA, bool PACKED, int PAIRS = 4, int MINB = 1>
 __global__ void __launch_bounds__(kBlockThreads, MINB)
@@ -51,7 +41,6 @@ render_paths(const __grid_constant__ KernelParams P) {
     __syncthreads();
 
     const unsigned lane = threadIdx.x & 31u;
-    const uint64_t plane = (uint64_t)P.width * P.height;
     const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
 
     uint32_t pix = kInvalidPixel, px = 0, py = 0;
@@ -102,22 +91,9 @@ render_paths(const __grid_constant__ KernelParams P) {
                 m = __ballot_sync(0xFFFFFFFFu, need);
             }
             if (!active && !done) {
-                // A1 primary ray, main.cpp:375-385; stream contract: SURVEY 8c P10
-                rng = stream_seed(P.stream_base + (uint64_t)k * plane + pix);
+                primary_ray(P, px, py, pix, k, rng, o, d);
                 atten = mk3(1.0f, 1.0f, 1.0f);
                 out = mk3(0.0f, 0.0f, 0.0f);
-                const float jx = rand_float(rng, kInvU32Range1, -0.5f);
-                const float jy = rand_float(rng, kInvU32Range1, -0.5f);
-                const float film_x = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)px, jx), 2.0f), (float)P.width));
-                const float film_y = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)py, jy), 2.0f), (float)P.height));
-                const float ax = __fmul_rn(__fmul_rn(film_x, P.cam.film_w), 0.5f);
-                const float ay = __fmul_rn(__fmul_rn(film_y, P.cam.film_h), 0.5f);
-                const f3 cam_x = mk3(P.cam.x[0], P.cam.x[1], P.cam.x[2]);
-                const f3 cam_y = mk3(P.cam.y[0], P.cam.y[1], P.cam.y[2]);
-                const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
-                const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
-                o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
-                d = normalize3(sub3(film_p, o));
                 bounce = 0;
                 active = true;
             }
@@ -135,65 +111,10 @@ render_paths(const __grid_constant__ KernelParams P) {
                 P.tap_t[pix] = h.t;
                 P.tap_prim[pix] = h.prim;
             }
-            bool path_end = false;
-            if (!h.hit) {
-                if (P.use_sky) {                                          // A5 main.cpp:433-440
-                    const float a = __fmul_rn(__fadd_rn(d.y, 1.0f), 0.5f);
-                    const float ia = __fsub_rn(1.0f, a);
-                    const f3 sky = add3(scale3(ia, mk3(1.0f, 1.0f, 1.0f)), scale3(a, mk3(0.5f, 0.7f, 1.0f)));
-                    out = add3(out, mul3(sky, atten));
-                }
-                path_end = true;
-            } else {
-                // ---- A6 shade + scatter, main.cpp:443-481 ---------------------------------
-                const DevMaterial *M = &P.materials[h.prim];
-                const float4 cs = __ldg(&M->color_spec);
-                const float4 ei = __ldg(&M->emis_ior);
-                const float4 dv = __ldg(&M->derived);
-                out = add3(out, mul3(mk3(ei.x, ei.y, ei.z), atten));
-                atten = mul3(atten, mk3(cs.x, cs.y, cs.z));
-                // winner's HitNormal / NextRayOrigin, recomputed with the ops of main.cpp:423-429
-                const float4 s = PACKED ? paired_sphere(s_spheres, h.prim) : s_spheres[h.prim];
-                const f3 sc = sub3(mk3(s.x, s.y, s.z), o);
-                const f3 ip = scale3(h.t, d);
-                o = add3(o, ip);
-                f3 n = normalize3(sub3(ip, sc));
-                const f3 pure = sub3(d, scale3(__fmul_rn(2.0f, dot3(d, n)), n));   // :453
-                if (h.inside) n = neg3(n);
-                if (ei.w == 0.0f) {
-                    const float rx = rand_float(rng, kInvU32Range2, -1.0f);
-                    const float ry = rand_float(rng, kInvU32Range2, -1.0f);
-                    const float rz = rand_float(rng, kInvU32Range2, -1.0f);
-                    const f3 r = normalize3(mk3(rx, ry, rz));                      // :461
-                    const f3 rb = add3(n, r);
-                    d = normalize3(add3(scale3(dv.x, rb), scale3(cs.w, pure)));    // :463-464
-                } else {
-                    const float eta = h.inside ? ei.w : dv.y;                      // :466
-                    const float cd = dot3(neg3(d), n);
-                    const float c = (cd < 1.0f) ? cd : 1.0f;                       // _mm_min_ss :468
-                    const float cc = __fmul_rn(c, c);
-                    const float sn = __fsqrt_rn(__double2float_rn(__dsub_rn(1.0, (double)cc)));   // :469
-                    const bool cant = __fmul_rn(eta, sn) > 1.0f;                   // :471
-                    const f3 perp = scale3(eta, add3(d, scale3(c, n)));            // :472
-                    const float kk = -__fsqrt_rn(fabsf(__fsub_rn(1.0f, dot3(perp, perp))));   // :473
-                    const f3 refr = normalize3(add3(perp, scale3(kk, n)));         // :474
-                    bool reflect = cant;                                            // :476 (|| short-circuit)
-                    if (!cant) reflect = reflectance(c, eta) > rand_float(rng, kInvU32Range1, 0.0f);
-                    d = (reflect && !h.inside) ? pure : refr;
-                }
-                bounce += 1;
-                path_end = (bounce == kMaxBounce);
-            }
-            if (path_end) {
-                if (P.accum_mode == SRT_ACCUM_MEAN) {
-                    // A8 running mean, main.cpp:484-489 (k == PreviousRayCount)
-                    const float total = (float)(k + 1u);
-                    const float wa = __fdiv_rn(1.0f, total);
-                    const float wb = __fdiv_rn((float)k, total);
-                    mean = add3(scale3(wa, out), scale3(wb, mean));
-                } else {
-                    mean = add3(mean, out);
-                }
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (h.hit) s = PACKED ? paired_sphere(s_spheres, h.prim) : s_spheres[h.prim];
+            if (shade_scatter(P, h, s, o, d, atten, out, rng, bounce)) {
+                mean = accumulate_sample(P.accum_mode, mean, out, k);
                 k += P.sample_stride;
                 active = false;
             }
@@ -207,8 +128,9 @@ render_paths(const __grid_constant__ KernelParams P) {
 
 // ------------------------------------------------------------------------------------------
 // render_pairs: the same pipeline A1..A9 with TWO paths per thread (slot 0 / slot 1) packed
-// into the halves of Blackwell's f32x2 instructions (srt_pairs.cuh).  Used for scenes large
-// enough for the intersection loop to dominate (>= kPairsMinSpheres).
+// into the halves of Blackwell's f32x2 instructions (srt_pairs.cuh: fused filter over all
+// spheres, reference arithmetic on the candidates).  Used when the intersection loop
+// dominates (>= kPairsMinSpheres spheres).
 //
 // Everything a path carries between bounces -- ray, attenuation, radiance, running mean, RNG
 // state, pixel, sample index -- is parked in shared memory (field-major, conflict-free), so
@@ -231,15 +153,12 @@ render_pairs(const __grid_constant__ KernelParams P) {
 #define SRT_ST(f, r) st[(((f) * THREADS) + tid) * 2 + (r)]
 #define SRT_SU(f, r) su[(((f) * THREADS) + tid) * 2 + (r)]
     for (uint32_t i = tid; i < P.n_pad; i += THREADS) { s_spheres[i] = P.spheres[i]; s_scan[i] = P.scan_table[i]; }
-    const uint64_t plane = (uint64_t)P.width * P.height;
     const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
         SRT_SU(S_PIX, r) = kInvalidPixel;
         SRT_SU(S_K, r) = k_end;
         SRT_SU(S_FLAGS, r) = 0u;
-        SRT_ST(S_OX, r) = kIdleOrigin; SRT_ST(S_OY, r) = kIdleOrigin; SRT_ST(S_OZ, r) = kIdleOrigin;
-        SRT_ST(S_DX, r) = 0.0f; SRT_ST(S_DY, r) = 0.0f; SRT_ST(S_DZ, r) = 0.0f;
     }
     __syncthreads();
     unsigned long long rays = 0;
@@ -283,32 +202,18 @@ render_pairs(const __grid_constant__ KernelParams P) {
                     }
                     m = __ballot_sync(0xFFFFFFFFu, need);
                 }
-                if (idle && !(flags & kFlagDone)) {
-                    // A1 primary ray, main.cpp:375-385; stream contract: SURVEY 8c P10
-                    uint64_t rng = stream_seed(P.stream_base + (uint64_t)k * plane + pix);
-                    const uint32_t px = pxy & 0xFFFFu, py = pxy >> 16;
-                    const float jx = rand_float(rng, kInvU32Range1, -0.5f);
-                    const float jy = rand_float(rng, kInvU32Range1, -0.5f);
-                    const float film_x = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)px, jx), 2.0f), (float)P.width));
-                    const float film_y = __fadd_rn(-1.0f, __fdiv_rn(__fmul_rn(__fadd_rn((float)py, jy), 2.0f), (float)P.height));
-                    const float ax = __fmul_rn(__fmul_rn(film_x, P.cam.film_w), 0.5f);
-                    const float ay = __fmul_rn(__fmul_rn(film_y, P.cam.film_h), 0.5f);
-                    const f3 cam_x = mk3(P.cam.x[0], P.cam.x[1], P.cam.x[2]);
-                    const f3 cam_y = mk3(P.cam.y[0], P.cam.y[1], P.cam.y[2]);
-                    const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
-                    const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
-                    const f3 o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
-                    const f3 d = normalize3(sub3(film_p, o));
+                if (idle) {
+                    f3 o = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin), d = mk3(0.0f, 0.0f, 0.0f);   // out of work: parked
+                    if (!(flags & kFlagDone)) {
+                        uint64_t rng;
+                        primary_ray(P, pxy & 0xFFFFu, pxy >> 16, pix, k, rng, o, d);
+                        SRT_ST(S_AX, r) = 1.0f; SRT_ST(S_AY, r) = 1.0f; SRT_ST(S_AZ, r) = 1.0f;
+                        SRT_ST(S_LX, r) = 0.0f; SRT_ST(S_LY, r) = 0.0f; SRT_ST(S_LZ, r) = 0.0f;
+                        SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
+                        flags = kFlagActive;                                           // bounce 0
+                    }
                     SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
                     SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
-                    SRT_ST(S_AX, r) = 1.0f; SRT_ST(S_AY, r) = 1.0f; SRT_ST(S_AZ, r) = 1.0f;
-                    SRT_ST(S_LX, r) = 0.0f; SRT_ST(S_LY, r) = 0.0f; SRT_ST(S_LZ, r) = 0.0f;
-                    SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
-                    flags = kFlagActive;                                           // bounce 0
-                } else if (idle) {
-                    // out of work: park the slot where no sphere can be a candidate
-                    SRT_ST(S_OX, r) = kIdleOrigin; SRT_ST(S_OY, r) = kIdleOrigin; SRT_ST(S_OZ, r) = kIdleOrigin;
-                    SRT_ST(S_DX, r) = 0.0f; SRT_ST(S_DY, r) = 0.0f; SRT_ST(S_DZ, r) = 0.0f;
                 }
                 SRT_SU(S_PIX, r) = pix; SRT_SU(S_K, r) = k; SRT_SU(S_PXY, r) = pxy; SRT_SU(S_FLAGS, r) = flags;
             }
@@ -332,86 +237,30 @@ render_pairs(const __grid_constant__ KernelParams P) {
             if (!(flags & kFlagActive)) continue;
             rays += 1;                                                        // main.cpp:390
             const Hit h = r ? h1 : h0;
-            const uint32_t pix = SRT_SU(S_PIX, r);
-            uint32_t k = SRT_SU(S_K, r);
+            const uint32_t k = SRT_SU(S_K, r);
             uint32_t bounce = flags & kFlagBounceMask;
             f3 o = mk3(SRT_ST(S_OX, r), SRT_ST(S_OY, r), SRT_ST(S_OZ, r));
             f3 d = mk3(SRT_ST(S_DX, r), SRT_ST(S_DY, r), SRT_ST(S_DZ, r));
             f3 atten = mk3(SRT_ST(S_AX, r), SRT_ST(S_AY, r), SRT_ST(S_AZ, r));
             f3 out = mk3(SRT_ST(S_LX, r), SRT_ST(S_LY, r), SRT_ST(S_LZ, r));
+            uint64_t rng = (uint64_t)SRT_SU(S_RNG_LO, r) | ((uint64_t)SRT_SU(S_RNG_HI, r) << 32);
             if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
+                const uint32_t pix = SRT_SU(S_PIX, r);
                 P.tap_t[pix] = h.t;
                 P.tap_prim[pix] = h.prim;
             }
-            bool path_end = false;
-            if (!h.hit) {
-                if (P.use_sky) {                                              // A5 main.cpp:433-440
-                    const float a = __fmul_rn(__fadd_rn(d.y, 1.0f), 0.5f);
-                    const float ia = __fsub_rn(1.0f, a);
-                    const f3 sky = add3(scale3(ia, mk3(1.0f, 1.0f, 1.0f)), scale3(a, mk3(0.5f, 0.7f, 1.0f)));
-                    out = add3(out, mul3(sky, atten));
-                }
-                path_end = true;
-            } else {
-                // ---- A6 shade + scatter, main.cpp:443-481 -------------------------------------
-                uint64_t rng = (uint64_t)SRT_SU(S_RNG_LO, r) | ((uint64_t)SRT_SU(S_RNG_HI, r) << 32);
-                const DevMaterial *M = &P.materials[h.prim];
-                const float4 cs = __ldg(&M->color_spec);
-                const float4 ei = __ldg(&M->emis_ior);
-                const float4 dv = __ldg(&M->derived);
-                out = add3(out, mul3(mk3(ei.x, ei.y, ei.z), atten));
-                atten = mul3(atten, mk3(cs.x, cs.y, cs.z));
-                // winner's HitNormal / NextRayOrigin, recomputed with the ops of main.cpp:423-429
-                const float4 s = s_spheres[h.prim];
-                const f3 sc = sub3(mk3(s.x, s.y, s.z), o);
-                const f3 ip = scale3(h.t, d);
-                o = add3(o, ip);
-                f3 n = normalize3(sub3(ip, sc));
-                const f3 pure = sub3(d, scale3(__fmul_rn(2.0f, dot3(d, n)), n));   // :453
-                if (h.inside) n = neg3(n);
-                if (ei.w == 0.0f) {
-                    const float rx = rand_float(rng, kInvU32Range2, -1.0f);
-                    const float ry = rand_float(rng, kInvU32Range2, -1.0f);
-                    const float rz = rand_float(rng, kInvU32Range2, -1.0f);
-                    const f3 rr = normalize3(mk3(rx, ry, rz));                     // :461
-                    const f3 rb = add3(n, rr);
-                    d = normalize3(add3(scale3(dv.x, rb), scale3(cs.w, pure)));    // :463-464
-                } else {
-                    const float eta = h.inside ? ei.w : dv.y;                      // :466
-                    const float cd = dot3(neg3(d), n);
-                    const float c = (cd < 1.0f) ? cd : 1.0f;                       // _mm_min_ss :468
-                    const float cc = __fmul_rn(c, c);
-                    const float sn = __fsqrt_rn(__double2float_rn(__dsub_rn(1.0, (double)cc)));   // :469
-                    const bool cant = __fmul_rn(eta, sn) > 1.0f;                   // :471
-                    const f3 perp = scale3(eta, add3(d, scale3(c, n)));            // :472
-                    const float kk = -__fsqrt_rn(fabsf(__fsub_rn(1.0f, dot3(perp, perp))));   // :473
-                    const f3 refr = normalize3(add3(perp, scale3(kk, n)));         // :474
-                    bool reflect = cant;                                            // :476 (|| short-circuit)
-                    if (!cant) reflect = reflectance(c, eta) > rand_float(rng, kInvU32Range1, 0.0f);
-                    d = (reflect && !h.inside) ? pure : refr;
-                }
-                bounce += 1;
-                path_end = (bounce == kMaxBounce);
-                SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
-                SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
-                SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
-                SRT_ST(S_AX, r) = atten.x; SRT_ST(S_AY, r) = atten.y; SRT_ST(S_AZ, r) = atten.z;
-            }
-            if (path_end) {
-                f3 mean = mk3(SRT_ST(S_MX, r), SRT_ST(S_MY, r), SRT_ST(S_MZ, r));
-                if (P.accum_mode == SRT_ACCUM_MEAN) {
-                    // A8 running mean, main.cpp:484-489 (k == PreviousRayCount)
-                    const float total = (float)(k + 1u);
-                    const float wa = __fdiv_rn(1.0f, total);
-                    const float wb = __fdiv_rn((float)k, total);
-                    mean = add3(scale3(wa, out), scale3(wb, mean));
-                } else {
-                    mean = add3(mean, out);
-                }
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (h.hit) s = s_spheres[h.prim];
+            if (shade_scatter(P, h, s, o, d, atten, out, rng, bounce)) {
+                const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, r), SRT_ST(S_MY, r), SRT_ST(S_MZ, r)), out, k);
                 SRT_ST(S_MX, r) = mean.x; SRT_ST(S_MY, r) = mean.y; SRT_ST(S_MZ, r) = mean.z;
                 SRT_SU(S_K, r) = k + P.sample_stride;
                 flags = 0u;                                                   // idle; regenerated next pass
             } else {
+                SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
+                SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
+                SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
+                SRT_ST(S_AX, r) = atten.x; SRT_ST(S_AY, r) = atten.y; SRT_ST(S_AZ, r) = atten.z;
                 SRT_ST(S_LX, r) = out.x; SRT_ST(S_LY, r) = out.y; SRT_ST(S_LZ, r) = out.z;
                 flags = kFlagActive | bounce;
             }
@@ -424,6 +273,69 @@ render_pairs(const __grid_constant__ KernelParams P) {
     // rays: one atomic per warp
     for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
     if (lane == 0 && rays) atomicAdd(P.rays, rays);
+}
+
+// ------------------------------------------------------------------------------------------
+// audit_filter: diagnostic kernel behind srt_filter_audit().  One path per thread (pixel),
+// advanced with the literal per-lane reference arithmetic; for EVERY (ray, sphere) pair of
+// every path segment it evaluates both the reference's hit predicate and the ray-pair
+// kernel's filter predicate (the very filter_ray / filter_sphere code) and counts
+//   tests, exact hits, filter candidates, and VIOLATIONS (exact hit that the filter rejects).
+// The filter is sound iff violations == 0.
+// ------------------------------------------------------------------------------------------
+template <int W, bool FMA>
+__global__ void __launch_bounds__(kBlockThreads)
+audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counters) {
+    unsigned long long n_tests = 0, n_hits = 0, n_cand = 0, n_viol = 0;
+    const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pix < P.width * P.height) {
+        const uint32_t px = pix % P.width, py = pix / P.width;
+        for (uint32_t k = P.first_sample; k < P.first_sample + P.n_samples; ++k) {
+            uint64_t rng;
+            f3 o, d, atten = mk3(1.0f, 1.0f, 1.0f), out = mk3(0.0f, 0.0f, 0.0f);
+            uint32_t bounce = 0;
+            primary_ray(P, px, py, pix, k, rng, o, d);
+            for (;;) {
+                const FilterRay f = filter_ray(o.x, o.y, o.z, d.x, d.y, d.z);
+                const pk2 p2ox = pk_make(f.p2ox, f.p2ox), p2oy = pk_make(f.p2oy, f.p2oy), p2oz = pk_make(f.p2oz, f.p2oz);
+                const pk2 fdx = pk_make(f.dx, f.dx), fdy = pk_make(f.dy, f.dy), fdz = pk_make(f.dz, f.dz), od = pk_make(f.od, f.od);
+                for (uint32_t i = 0; i < P.n_pad; ++i) {
+                    const float4 s = P.spheres[i];
+                    const float scx = __fsub_rn(s.x, o.x), scy = __fsub_rn(s.y, o.y), scz = __fsub_rn(s.z, o.z);
+                    const float t = lane_dot<(W != 1) && FMA>(scx, scy, scz, d.x, d.y, d.z);
+                    const float vx = __fsub_rn(scx, __fmul_rn(d.x, t));
+                    const float vy = __fsub_rn(scy, __fmul_rn(d.y, t));
+                    const float vz = __fsub_rn(scz, __fmul_rn(d.z, t));
+                    const float d2 = lane_dot<(W != 1) && FMA>(vx, vy, vz, vx, vy, vz);
+                    const bool exact = (W == 1) ? (!(d2 > s.w) && i < P.n_spheres) : (d2 < s.w);
+                    uint32_t mask = 0;
+                    filter_sphere(mask, 1u, P.scan_table[i], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, f.oo, f.oo);
+                    n_tests += 1;
+                    n_hits += exact ? 1 : 0;
+                    n_cand += mask;
+                    n_viol += (exact && !mask) ? 1 : 0;
+                }
+                Hit h;
+                if (W == 1) h = intersect_scalar(P.spheres, P.n_pad, P.n_spheres, o, d);
+                else h = intersect_lanes<(W == 1 ? 4 : W), FMA>(P.spheres, P.n_pad, o, d);
+                float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (h.hit) s = P.spheres[h.prim];
+                if (shade_scatter(P, h, s, o, d, atten, out, rng, bounce)) break;
+            }
+        }
+    }
+    for (int off = 16; off > 0; off >>= 1) {
+        n_tests += __shfl_down_sync(0xFFFFFFFFu, n_tests, off);
+        n_hits += __shfl_down_sync(0xFFFFFFFFu, n_hits, off);
+        n_cand += __shfl_down_sync(0xFFFFFFFFu, n_cand, off);
+        n_viol += __shfl_down_sync(0xFFFFFFFFu, n_viol, off);
+    }
+    if ((threadIdx.x & 31u) == 0) {
+        atomicAdd(&counters[0], n_tests);
+        atomicAdd(&counters[1], n_hits);
+        atomicAdd(&counters[2], n_cand);
+        atomicAdd(&counters[3], n_viol);
+    }
 }
 
 // mean = sum * (1/N); tonemap + pack.  HBM-bound: 16 B read + 16 B + 4 B written per pixel.
@@ -692,28 +604,20 @@ int srt_bind_device_buffers(srt_backend *b, void *accum_dev, void *rgba_dev) {
     return SRT_OK;
 }
 
-int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *args) {
-    if (!b) return SRT_ERR_INVALID;
-    if (!cam || !args) return fail(b, SRT_ERR_INVALID, "srt_render: null argument");
-    if (!b->d_spheres) return fail(b, SRT_ERR_INVALID, "srt_render: no scene (call srt_set_scene)");
-    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_render: no image (call srt_resize)");
-    if (args->n_samples == 0 || args->sample_stride == 0) return fail(b, SRT_ERR_INVALID, "srt_render: n_samples and sample_stride must be >= 1");
-    if (args->accum_mode != SRT_ACCUM_MEAN && args->accum_mode != SRT_ACCUM_SUM) return fail(b, SRT_ERR_INVALID, "srt_render: bad accum_mode");
+// Argument checks + the fields every kernel shares.
+static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_args *args, const char *who, KernelParams &P) {
+    const std::string w(who);
+    if (!cam || !args) return fail(b, SRT_ERR_INVALID, w + ": null argument");
+    if (!b->d_spheres) return fail(b, SRT_ERR_INVALID, w + ": no scene (call srt_set_scene)");
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, w + ": no image (call srt_resize)");
+    if (args->n_samples == 0 || args->sample_stride == 0) return fail(b, SRT_ERR_INVALID, w + ": n_samples and sample_stride must be >= 1");
+    if (args->accum_mode != SRT_ACCUM_MEAN && args->accum_mode != SRT_ACCUM_SUM) return fail(b, SRT_ERR_INVALID, w + ": bad accum_mode");
     if (args->accum_mode == SRT_ACCUM_MEAN && args->sample_stride != 1)
-        return fail(b, SRT_ERR_INVALID, "srt_render: the exact running mean needs contiguous samples (sample_stride == 1)");
+        return fail(b, SRT_ERR_INVALID, w + ": the exact running mean needs contiguous samples (sample_stride == 1)");
     if ((uint64_t)args->first_sample + (uint64_t)args->n_samples * args->sample_stride > 0xFFFFFFFFull)
-        return fail(b, SRT_ERR_INVALID, "srt_render: sample index overflows 32 bits");
-    SRT_CUDA(b, cudaSetDevice(b->device));
-    int rc = drain(b);
-    if (rc) return rc;
-
-    KernelParams P;
+        return fail(b, SRT_ERR_INVALID, w + ": sample index overflows 32 bits");
     memset(&P, 0, sizeof(P));
-    const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad) <= b->max_smem_optin;
-    const bool pairs = pairs_fit && (b->variant == 8 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
-    if (b->variant == 8 && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
-    const bool packed = !pairs && (b->variant != 1) && b->opt.lane_width != 1;
-    P.spheres = packed ? b->d_spheres2 : b->d_spheres;
+    P.spheres = b->d_spheres;
     P.scan_table = b->d_scan;
     P.regen_threshold = b->regen_threshold;
     P.neg_one = -1.0f;
@@ -741,6 +645,25 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     P.stream_base = args->stream_base;
     P.accum = b->d_accum;
     P.rgba = b->d_rgba;
+    P.rays = (unsigned long long *)b->d_counters;
+    P.work_counter = (unsigned int *)(b->d_counters + 8);
+    return SRT_OK;
+}
+
+int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *args) {
+    if (!b) return SRT_ERR_INVALID;
+    KernelParams P;
+    int rc = make_params(b, cam, args, "srt_render", P);
+    if (rc) return rc;
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    rc = drain(b);
+    if (rc) return rc;
+
+    const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad) <= b->max_smem_optin;
+    const bool pairs = pairs_fit && (b->variant == 8 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
+    if (b->variant == 8 && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
+    const bool packed = !pairs && (b->variant != 1) && b->opt.lane_width != 1;
+    if (packed) P.spheres = b->d_spheres2;
     if (args->record_primary) {
         const size_t n = (size_t)b->width * b->height;
         if (!b->d_tap_prim) {
@@ -751,8 +674,6 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         P.tap_t = b->d_tap_t;
         b->tap_valid = true;
     }
-    P.rays = (unsigned long long *)b->d_counters;
-    P.work_counter = (unsigned int *)(b->d_counters + 8);
 
     render_kernel_t kernel = pairs ? pick_pairs_kernel(b->opt) : pick_kernel(b->opt, packed, b->variant);
     const int threads = pairs ? kPairThreads : kBlockThreads;
@@ -797,6 +718,38 @@ int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays) {
         *out_ms = ms;
     }
     if (out_rays) *out_rays = *b->h_rays;
+    return SRT_OK;
+}
+
+int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_args *args, uint64_t out_counts[4]) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!out_counts) return fail(b, SRT_ERR_INVALID, "srt_filter_audit: null output");
+    KernelParams P;
+    int rc = make_params(b, cam, args, "srt_filter_audit", P);
+    if (rc) return rc;
+    if (args->sample_stride != 1) return fail(b, SRT_ERR_INVALID, "srt_filter_audit: sample_stride must be 1");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    rc = drain(b);
+    if (rc) return rc;
+    unsigned long long *d_cnt = nullptr;
+    SRT_CUDA(b, cudaMalloc(&d_cnt, 4 * sizeof(unsigned long long)));
+    SRT_CUDA(b, cudaMemsetAsync(d_cnt, 0, 4 * sizeof(unsigned long long), b->stream));
+    const uint32_t n = b->width * b->height;
+    const dim3 grid((n + kBlockThreads - 1) / kBlockThreads);
+    const srt_scene_options &o = b->opt;
+    if (o.lane_width == 1) audit_filter<1, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+    else if (o.lane_width == 4 && o.fma_dot) audit_filter<4, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+    else if (o.lane_width == 4) audit_filter<4, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+    else if (o.fma_dot) audit_filter<8, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+    else audit_filter<8, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+    cudaError_t e = cudaGetLastError();
+    unsigned long long h[4] = {0, 0, 0, 0};
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, b->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+    cudaFree(d_cnt);
+    if (e != cudaSuccess) return fail(b, SRT_ERR_CUDA, std::string("srt_filter_audit: ") + cudaGetErrorString(e));
+    for (int i = 0; i < 4; ++i) out_counts[i] = h[i];
+    b->launches += 1;
     return SRT_OK;
 }
 

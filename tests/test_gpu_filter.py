@@ -1,0 +1,169 @@
+"""GPU: the ray-pair kernel (csrc/srt_pairs.cuh) -- a conservative fused-arithmetic sphere
+filter followed by the reference's exact arithmetic on the survivors.
+
+Three kinds of evidence that the filter never changes a result:
+  1. srt_filter_audit: for every (path segment, sphere) pair of whole renders, the reference's
+     hit predicate implies the filter predicate (violations == 0), on the built-in scenes, the
+     synthetic 1,024-sphere scene and on adversarial scenes (large coordinates, tiny spheres,
+     far camera).
+  2. The ray-pair kernel and the sphere-pair kernel (literal reference arithmetic for every
+     sphere) give bit-identical buffers at sizes the CPU oracle would take too long for.
+  3. Scenes built to trigger the rare paths (sticky InsideSphere replay, exact t ties, rays
+     starting inside several spheres) match the CPU oracle bit for bit in every mode.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+MODES = [(8, 1), (4, 0), (1, 0)]   # (lane_width, fma_dot)
+
+
+def _render(backend, spheres, sky, W, fma, cam, w, h, n, first=0):
+    backend.set_scene(spheres, sky, W, bool(fma))
+    backend.resize(w, h)
+    backend.render(cam, first, n, record_primary=True)
+    ms, rays = backend.wait()
+    prim, t = backend.read_primary()
+    return dict(accum=backend.read_accum(), rgba=backend.read_rgba8(), prim=prim, t=t, rays=rays)
+
+
+def _same(a, b):
+    bad = {k: int((a[k].view(np.uint32) != b[k].view(np.uint32)).sum()) for k in ("accum", "rgba", "prim", "t")
+           if not np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32))}
+    if a["rays"] != b["rays"]:
+        bad["rays"] = (a["rays"], b["rays"])
+    return bad
+
+
+def _mk(srt, rows):
+    """rows: (x, y, z, radius, (r,g,b), (er,eg,eb), specular, ior)"""
+    sp = np.zeros(len(rows), srt.sphere_dtype)
+    for i, (x, y, z, r, col, em, spec, ior) in enumerate(rows):
+        sp["position"][i, :3] = (x, y, z)
+        sp["radius"][i] = r
+        sp["color"][i, :3] = col
+        sp["emissive"][i, :3] = em
+        sp["specular"][i] = spec
+        sp["ior"][i] = ior
+    return sp
+
+
+@pytest.mark.parametrize("scene", [1, 2, 3])
+@pytest.mark.parametrize("mode", MODES)
+def test_filter_audit_scenes(backend, srt, scene, mode):
+    W, fma = mode
+    spheres, sky, hdr = srt.host_scene(scene)
+    w, h = (96, 54) if scene == 3 else (160, 90)
+    cam = srt.host_camera(scene, w, h, hdr)
+    backend.set_scene(spheres, sky, W, bool(fma))
+    backend.resize(w, h)
+    a = backend.filter_audit(cam, 0, 2)
+    assert a["tests"] > 0 and a["hits"] > 0
+    assert a["violations"] == 0, a
+    assert a["candidates"] >= a["hits"]
+    assert a["candidates"] < 4 * a["hits"] + a["tests"] // 500, a   # the filter stays selective
+
+
+def _shifted(spheres, cam, off):
+    s, c = spheres.copy(), cam.copy()
+    s["position"][:, :3] += np.float32(off)
+    c["position"][0, :3] += np.float32(off)
+    c["film_center"][0, :3] += np.float32(off)
+    return s, c
+
+
+@pytest.mark.parametrize("off", [300.0, 5000.0, -40000.0])
+def test_filter_audit_large_coordinates(backend, srt, oracle, off):
+    """The filter's error terms grow with |C|^2 + |O|^2: translate a scene far from the origin.
+    It must stay sound (only less selective) and the image must still equal the oracle's."""
+    spheres, sky, hdr = srt.host_scene(1)
+    w, h = 64, 36
+    s2, c2 = _shifted(spheres, srt.host_camera(1, w, h, hdr), off)
+    backend.set_scene(s2, sky, 8, True)
+    backend.resize(w, h)
+    a = backend.filter_audit(c2, 0, 2)
+    assert a["violations"] == 0, a
+    o = oracle.render(s2, sky, 8, 1, c2, w, h, 0, 2)
+    g = _render(backend, s2, sky, 8, 1, c2, w, h, 2)
+    assert _same(o, g) == {}
+
+
+def test_filter_audit_tiny_far_spheres(backend, srt, oracle):
+    """Small spheres seen from far away: r^2 is orders of magnitude below the rounding noise of
+    |C|^2 and |O|^2, the regime where a badly bounded filter would drop grazing hits."""
+    rng = np.random.default_rng(7)
+    rows = [(0.0, -1000.0, 0.0, 1000.0, (0.5, 0.5, 0.5), (0, 0, 0), 0.0, 0.0)]
+    for i in range(199):
+        x, z = rng.uniform(-40, 40, 2)
+        r = float(rng.uniform(0.01, 0.3))
+        kind = i % 4
+        rows.append((float(x), r, float(z), r, tuple(rng.uniform(0.2, 1, 3)), (2, 2, 2) if kind == 0 else (0, 0, 0),
+                     1.0 if kind == 1 else 0.0, 1.5 if kind == 2 else 0.0))
+    sp = _mk(srt, rows)
+    w, h = 96, 54
+    cam = np.zeros(1, srt.camera_dtype)
+    # camera 900 units away looking at the cluster through a narrow film
+    pos = np.array([0.0, 300.0, 850.0], np.float32)
+    zdir = pos / np.linalg.norm(pos)
+    xdir = np.cross([0, 1, 0], zdir); xdir /= np.linalg.norm(xdir)
+    ydir = np.cross(zdir, xdir)
+    cam["position"][0, :3] = pos; cam["z"][0, :3] = zdir; cam["x"][0, :3] = xdir; cam["y"][0, :3] = ydir
+    cam["film_center"][0, :3] = pos - zdir.astype(np.float32)
+    cam["film_w"][0] = 0.1; cam["film_h"][0] = 0.1 * h / w
+    for W, fma in MODES:
+        backend.set_scene(sp, True, W, bool(fma))
+        backend.resize(w, h)
+        a = backend.filter_audit(cam, 0, 2)
+        assert a["hits"] > 0 and a["violations"] == 0, (W, fma, a)
+        o = oracle.render(sp, True, W, fma, cam, w, h, 0, 2)
+        g = _render(backend, sp, True, W, fma, cam, w, h, 2)
+        assert _same(o, g) == {}, (W, fma)
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_pair_kernel_equals_sphere_pair_kernel(backend, srt, monkeypatch, mode):
+    """1,024-sphere scene, 480x270, 4 spp, all bounces: the filter+select kernel and the kernel
+    that runs the reference's arithmetic on every sphere agree on every bit."""
+    W, fma = mode
+    spheres, sky, hdr = srt.host_scene(3)
+    w, h = 480, 270
+    cam = srt.host_camera(3, w, h, hdr)
+    monkeypatch.setenv("SRT_KERNEL_VARIANT", "7")     # sphere-pair / scalar kernel, one path per thread
+    ref = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
+    monkeypatch.setenv("SRT_KERNEL_VARIANT", "8")     # ray-pair kernel
+    new = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
+    monkeypatch.delenv("SRT_KERNEL_VARIANT")
+    assert _same(ref, new) == {}
+    assert ref["rays"] > w * h * 4
+
+
+@pytest.mark.parametrize("mode", [(8, 1), (4, 0), (1, 0), (8, 0), (4, 1)])
+def test_nested_and_tied_spheres(backend, srt, oracle, mode):
+    """Rare paths of the select step: rays that start inside several nested glass spheres whose
+    indices share a SIMD lane (sticky InsideSphere, main.cpp:425 -> replay_inside), duplicated
+    spheres (exact t ties across lanes and groups), and a sphere enclosing the camera."""
+    W, fma = mode
+    glass = ((1, 1, 1), (0, 0, 0), 0.0, 1.5)
+    rows = [(0.0, -100.5, -1.0, 100.0, (0.8, 0.8, 0.0), (0, 0, 0), 0.0, 0.0)]          # 0 ground
+    rows += [(0.0, 0.0, -1.0, 0.9, *glass)]                                             # 1 outer glass
+    rows += [(50.0 + i, 50.0, 50.0, 0.1, (0.5, 0.5, 0.5), (0, 0, 0), 0.0, 0.0) for i in range(7)]   # 2..8 filler
+    rows += [(0.0, 0.0, -1.0, 0.5, *glass)]                                             # 9: same lane as 1 (W=8 and 4)
+    rows += [(0.2, 0.1, -1.0, 0.2, (0.9, 0.2, 0.2), (1, 1, 1), 0.0, 0.0)]               # 10 emissive core
+    rows += [(60.0 + i, 50.0, 50.0, 0.1, (0.5, 0.5, 0.5), (0, 0, 0), 0.0, 0.0) for i in range(6)]   # 11..16 filler
+    rows += [(0.0, 0.0, -1.0, 0.3, *glass)]                                             # 17: lane of 1 and 9 again
+    rows += [(-1.4, 0.0, -1.0, 0.5, (0.8, 0.6, 0.2), (0, 0, 0), 1.0, 0.0)] * 3          # 18..20 exact duplicates (ties)
+    rows += [(1.4, 0.0, -1.0, 0.5, (0.1, 0.2, 0.5), (0, 0, 0), 0.0, 0.0)] * 2           # 21..22 duplicates
+    rows += [(0.0, 0.0, 0.0, 30.0, *glass)]                                             # 23 encloses the camera
+    rows += [(70.0 + i, 50.0, 50.0, 0.1, (0.5, 0.5, 0.5), (0, 0, 0), 0.0, 0.0) for i in range(48)]  # pad to >= 64 spheres
+    sp = _mk(srt, rows)
+    w, h = 96, 54
+    cam = np.zeros(1, srt.camera_dtype)
+    cam["position"][0, :3] = (0, 0, 1.5); cam["z"][0, :3] = (0, 0, 1); cam["x"][0, :3] = (1, 0, 0); cam["y"][0, :3] = (0, 1, 0)
+    cam["film_center"][0, :3] = (0, 0, 0.5); cam["film_w"][0] = 1.0; cam["film_h"][0] = h / w
+    o = oracle.render(sp, True, W, fma, cam, w, h, 0, 3)
+    g = _render(backend, sp, True, W, fma, cam, w, h, 3)
+    assert _same(o, g) == {}
+    backend.set_scene(sp, True, W, bool(fma))
+    a = backend.filter_audit(cam, 0, 2)
+    assert a["violations"] == 0, a
