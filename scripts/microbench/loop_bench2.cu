@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(THREADS) kern(const float4 *sph, uint32_t n_pa
         if (MODE == 0) { Hit h = intersect_lanes_packed<8, true, 4>(s_sph, n_pad, o, d, neg1, one); acc += h.t; }
         if (MODE == 1) {
             Hit h0, h1;
-            intersect_pair<8, true>(s_scan, s_sph, n_pad, n_pad,
+            intersect_pair<8, true>(s_scan, (const float *)s_sph, sph, n_pad, n_pad,
                                     pk_make(o.x, o.x + 0.5f), pk_make(o.y, o.y), pk_make(o.z, o.z),
                                     pk_make(d.x, d.x), pk_make(d.y, d.y), pk_make(d.z, d.z), neg1, one, h0, h1);
             acc += h0.t + h1.t;

@@ -144,15 +144,15 @@ constexpr uint32_t kFlagBounceMask = 7u, kFlagActive = 8u, kFlagDone = 16u;
 template <int W, bool FMA, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
 render_pairs(const __grid_constant__ KernelParams P) {
-    extern __shared__ float4 s_spheres[];
-    float4 *const s_scan = s_spheres + P.n_pad;
-    float *const st = reinterpret_cast<float *>(s_scan + P.n_pad);
+    extern __shared__ float4 s_scan[];                     // {cx,cy,cz,-kappa}: centres + filter constant
+    float *const s_r2 = reinterpret_cast<float *>(s_scan + P.n_pad);
+    float *const st = s_r2 + P.n_pad;
     uint32_t *const su = reinterpret_cast<uint32_t *>(st);
     const uint32_t tid = threadIdx.x;
     const unsigned lane = tid & 31u;
 #define SRT_ST(f, r) st[(((f) * THREADS) + tid) * 2 + (r)]
 #define SRT_SU(f, r) su[(((f) * THREADS) + tid) * 2 + (r)]
-    for (uint32_t i = tid; i < P.n_pad; i += THREADS) { s_spheres[i] = P.spheres[i]; s_scan[i] = P.scan_table[i]; }
+    for (uint32_t i = tid; i < P.n_pad; i += THREADS) { s_scan[i] = P.scan_table[i]; s_r2[i] = P.spheres[i].w; }
     const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
 #pragma unroll
     for (int r = 0; r < 2; ++r) {
@@ -227,7 +227,7 @@ render_pairs(const __grid_constant__ KernelParams P) {
             const pk2 *const ray = reinterpret_cast<const pk2 *>(st);
             const pk2 ox = ray[S_OX * THREADS + tid], oy = ray[S_OY * THREADS + tid], oz = ray[S_OZ * THREADS + tid];
             const pk2 dx = ray[S_DX * THREADS + tid], dy = ray[S_DY * THREADS + tid], dz = ray[S_DZ * THREADS + tid];
-            intersect_pair<W, FMA>(s_scan, s_spheres, P.n_pad, P.n_spheres, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, h0, h1);
+            intersect_pair<W, FMA>(s_scan, s_r2, P.spheres, P.n_pad, P.n_spheres, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, h0, h1);
         }
 
         // ---- shade / scatter, one slot after the other ---------------------------------------
@@ -250,7 +250,7 @@ render_pairs(const __grid_constant__ KernelParams P) {
                 P.tap_prim[pix] = h.prim;
             }
             float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (h.hit) s = s_spheres[h.prim];
+            if (h.hit) s = s_scan[h.prim];                                    // centre only; .w is not used by shading
             if (shade_scatter(P, h, s, o, d, atten, out, rng, bounce)) {
                 const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, r), SRT_ST(S_MY, r), SRT_ST(S_MZ, r)), out, k);
                 SRT_ST(S_MX, r) = mean.x; SRT_ST(S_MY, r) = mean.y; SRT_ST(S_MZ, r) = mean.z;
@@ -421,17 +421,30 @@ static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed, int 
 }
 
 // Ray-pair kernel (srt_pairs.cuh): used when the scene is large enough for the intersection
-// loop to dominate and small enough for both sphere tables to stay resident in shared memory.
+// loop to dominate and small enough for the sphere tables to stay resident in shared memory.
 constexpr int kPairThreads = 256;
 constexpr int kPairMinBlocks = 2;
 constexpr uint32_t kPairsMinSpheres = 64;
-static render_kernel_t pick_pairs_kernel(const srt_scene_options &o) {
-    if (o.lane_width == 1) return render_pairs<1, false, kPairThreads, kPairMinBlocks>;
-    if (o.lane_width == 4) return o.fma_dot ? render_pairs<4, true, kPairThreads, kPairMinBlocks> : render_pairs<4, false, kPairThreads, kPairMinBlocks>;
-    return o.fma_dot ? render_pairs<8, true, kPairThreads, kPairMinBlocks> : render_pairs<8, false, kPairThreads, kPairMinBlocks>;
+struct PairConfig { int threads; render_kernel_t kernel; };
+static PairConfig pick_pairs_kernel(const srt_scene_options &o, int tuning) {
+    if (tuning > 0 && o.lane_width == 8 && o.fma_dot) {    // SRT_PAIR_CONFIG: occupancy experiments (W=8, FMA only)
+        switch (tuning) {
+            case 1: return {256, render_pairs<8, true, 256, 3>};
+            case 2: return {512, render_pairs<8, true, 512, 1>};
+            case 3: return {512, render_pairs<8, true, 512, 2>};
+            case 4: return {128, render_pairs<8, true, 128, 4>};
+            case 5: return {128, render_pairs<8, true, 128, 6>};
+            case 6: return {128, render_pairs<8, true, 128, 8>};
+            case 7: return {256, render_pairs<8, true, 256, 4>};
+            default: break;
+        }
+    }
+    if (o.lane_width == 1) return {kPairThreads, render_pairs<1, false, kPairThreads, kPairMinBlocks>};
+    if (o.lane_width == 4) return {kPairThreads, o.fma_dot ? render_pairs<4, true, kPairThreads, kPairMinBlocks> : render_pairs<4, false, kPairThreads, kPairMinBlocks>};
+    return {kPairThreads, o.fma_dot ? render_pairs<8, true, kPairThreads, kPairMinBlocks> : render_pairs<8, false, kPairThreads, kPairMinBlocks>};
 }
-static size_t pairs_smem_bytes(uint32_t n_pad) {
-    return (size_t)n_pad * 2 * sizeof(float4) + (size_t)S_COUNT * 2 * kPairThreads * sizeof(float);
+static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
+    return (size_t)n_pad * (sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * 2 * threads * sizeof(float);
 }
 
 extern "C" {
@@ -659,7 +672,10 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     rc = drain(b);
     if (rc) return rc;
 
-    const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad) <= b->max_smem_optin;
+    int pair_tuning = 0;
+    if (const char *t = getenv("SRT_PAIR_CONFIG")) pair_tuning = atoi(t);
+    const PairConfig pc = pick_pairs_kernel(b->opt, pair_tuning);
+    const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad, pc.threads) <= b->max_smem_optin;
     const bool pairs = pairs_fit && (b->variant == 8 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
     if (b->variant == 8 && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
     const bool packed = !pairs && (b->variant != 1) && b->opt.lane_width != 1;
@@ -675,9 +691,9 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         b->tap_valid = true;
     }
 
-    render_kernel_t kernel = pairs ? pick_pairs_kernel(b->opt) : pick_kernel(b->opt, packed, b->variant);
-    const int threads = pairs ? kPairThreads : kBlockThreads;
-    const size_t smem = pairs ? pairs_smem_bytes(b->n_pad) : (size_t)b->n_pad * sizeof(float4);
+    render_kernel_t kernel = pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
+    const int threads = pairs ? pc.threads : kBlockThreads;
+    const size_t smem = pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));

@@ -120,19 +120,21 @@ __device__ __forceinline__ void filter_sphere(uint32_t &mask, uint32_t bit, cons
 }
 
 // Scan + select for the two rays of a thread.
-//   scan : shared memory, n_pad x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
-//   sph  : shared memory, n_pad x {cx, cy, cz, r2}     (the reference's operands, padding zero)
+//   scan       : shared memory, n_pad x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
+//   r2tab      : shared memory, n_pad x r2 (the reference's R*R, main.cpp:406; padding zero)
+//   sph_global : global memory, n_pad x {cx, cy, cz, r2}, only read by the rare replay_inside
 //   o*/d*: packed {slot0, slot1} origins and directions
-// The candidate bitmap (bit 31 - j of word c = sphere 32 c + j) lives in LOCAL memory on
-// purpose: ptxas cannot prove that a shared-memory store does not alias the sphere tables and
-// would serialise the next LDS.128 behind it.  One STL per 32 spheres.
+// The scan builds one 32-bit candidate mask per chunk of 32 spheres (bit 31 - j = sphere j of
+// the chunk) and appends the non-empty ones to a per-thread queue.  The queue lives in LOCAL
+// memory on purpose: ptxas cannot prove that a shared-memory store does not alias the sphere
+// tables and would serialise the next LDS.128 behind it.  One predicated STL.64 per chunk.
 template <int W, bool FMA>
-__device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float4 *__restrict__ sph,
-                                               uint32_t n_pad, uint32_t n_real,
+__device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
+                                               const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
                                                pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
                                                float neg_one_f, float one_f, Hit &h0, Hit &h1) {
-    uint32_t bitmap[kPairsMaxWords];
-    const uint32_t n_words = (n_pad + 31u) >> 5;
+    uint2 queue[kPairsMaxWords];      // {candidate mask, first sphere} of the 32-sphere chunks that have candidates
+    uint32_t qn = 0;
     {
         // ---- scan: every sphere, both rays, fused arithmetic, branch-free --------------------
         float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
@@ -149,7 +151,7 @@ __device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, 
             const float4 *blk = scan + (c << 5);
 #pragma unroll
             for (int j = 0; j < 32; ++j) filter_sphere(mask, 0x80000000u >> j, blk[j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
-            bitmap[c] = mask;
+            if (mask) { queue[qn] = make_uint2(mask, c << 5); qn += 1; }
         }
         if (n_pad & 31u) {                       // tail: 1..3 blocks of 8
             uint32_t mask = 0;
@@ -159,38 +161,44 @@ __device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, 
 #pragma unroll
                 for (int j = 0; j < 8; ++j) filter_sphere(mask, bit0 >> j, scan[base + j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
             }
-            bitmap[full] = mask;
+            if (mask) { queue[qn] = make_uint2(mask, full << 5); qn += 1; }
         }
     }
     // ---- select: the reference's arithmetic on the candidates, in index order ----------------
     const pk2 neg_one = pk_make(neg_one_f, neg_one_f), one = pk_make(one_f, one_f);
     Best b0 = best_init(), b1 = best_init();
-    for (uint32_t c = 0; c < n_words; ++c) {
-        uint32_t m = bitmap[c];
-        while (m) {
-            const uint32_t j = (uint32_t)__clz((int)m);
-            m &= ~(0x80000000u >> j);
-            const uint32_t idx = (c << 5) + j;
-            const float4 s = sph[idx];
-            const pk2 scx = pk_sub(pk_make(s.x, s.x), ox);                         // main.cpp:401
-            const pk2 scy = pk_sub(pk_make(s.y, s.y), oy);
-            const pk2 scz = pk_sub(pk_make(s.z, s.z), oz);
-            const pk2 t2 = pk_dot<FMA>(scx, scy, scz, dx, dy, dz, one);            // :402
-            const pk2 vx = pk_fma(pk_mul(dx, t2), neg_one, scx);                   // :403,407
-            const pk2 vy = pk_fma(pk_mul(dy, t2), neg_one, scy);
-            const pk2 vz = pk_fma(pk_mul(dz, t2), neg_one, scz);
-            const pk2 dd = pk_dot<FMA>(vx, vy, vz, vx, vy, vz, one);
-            float d2a, d2b, ta, tb;
-            pk_split(dd, d2a, d2b);
-            pk_split(t2, ta, tb);
-            if (W == 1) {
-                // `d2 > r2 -> continue` (:557) lets NaN through, so padding is excluded by index.
-                if (!(d2a > s.w) && idx < n_real) best_update<W>(b0, ta, d2a, s.w, idx);
-                if (!(d2b > s.w) && idx < n_real) best_update<W>(b1, tb, d2b, s.w, idx);
-            } else {
-                if (d2a < s.w) best_update<W>(b0, ta, d2a, s.w, idx);              // :409
-                if (d2b < s.w) best_update<W>(b1, tb, d2b, s.w, idx);
-            }
+    // Flattened over the thread's own candidates: the warp iterates max-over-lanes(candidates)
+    // times, not once per chunk that has a candidate in any lane.
+    uint32_t qi = 0, m = 0, first = 0;
+    for (;;) {
+        if (m == 0) {
+            if (qi == qn) break;
+            const uint2 e = queue[qi++];
+            m = e.x; first = e.y;
+        }
+        const uint32_t j = (uint32_t)__clz((int)m);
+        m &= ~(0x80000000u >> j);
+        const uint32_t idx = first + j;
+        float4 s = scan[idx];
+        s.w = r2tab[idx];
+        const pk2 scx = pk_sub(pk_make(s.x, s.x), ox);                         // main.cpp:401
+        const pk2 scy = pk_sub(pk_make(s.y, s.y), oy);
+        const pk2 scz = pk_sub(pk_make(s.z, s.z), oz);
+        const pk2 t2 = pk_dot<FMA>(scx, scy, scz, dx, dy, dz, one);            // :402
+        const pk2 vx = pk_fma(pk_mul(dx, t2), neg_one, scx);                   // :403,407
+        const pk2 vy = pk_fma(pk_mul(dy, t2), neg_one, scy);
+        const pk2 vz = pk_fma(pk_mul(dz, t2), neg_one, scz);
+        const pk2 dd = pk_dot<FMA>(vx, vy, vz, vx, vy, vz, one);
+        float d2a, d2b, ta, tb;
+        pk_split(dd, d2a, d2b);
+        pk_split(t2, ta, tb);
+        if (W == 1) {
+            // `d2 > r2 -> continue` (:557) lets NaN through, so padding is excluded by index.
+            if (!(d2a > s.w) && idx < n_real) best_update<W>(b0, ta, d2a, s.w, idx);
+            if (!(d2b > s.w) && idx < n_real) best_update<W>(b1, tb, d2b, s.w, idx);
+        } else {
+            if (d2a < s.w) best_update<W>(b0, ta, d2a, s.w, idx);              // :409
+            if (d2b < s.w) best_update<W>(b1, tb, d2b, s.w, idx);
         }
     }
     h0.t = b0.t; h0.hit = !(b0.t == kMax); h0.prim = h0.hit ? b0.idx : 0xFFFFFFFFu; h0.inside = b0.test != 0;
@@ -202,8 +210,8 @@ __device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, 
             float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
             pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
             pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
-            if (amb0) h0.inside = replay_inside<W, FMA>(sph, n_pad, oxa, oya, oza, dxa, dya, dza) != 0;
-            if (amb1) h1.inside = replay_inside<W, FMA>(sph, n_pad, oxb, oyb, ozb, dxb, dyb, dzb) != 0;
+            if (amb0) h0.inside = replay_inside<W, FMA>(sph_global, n_pad, oxa, oya, oza, dxa, dya, dza) != 0;
+            if (amb1) h1.inside = replay_inside<W, FMA>(sph_global, n_pad, oxb, oyb, ozb, dxb, dyb, dzb) != 0;
         }
     }
 }
