@@ -307,14 +307,23 @@ def run_gpu_arm(args):
     peak_tflops = info0["sm_count"] * 128 * 2 * sm_max_mhz * 1e6 / 1e12
     rays_per_launch = float(np.mean(kernel_rays))
     achieved = FLOP_PER_TEST * rays_per_launch * n_pad / (kms * 1e-3) / 1e12
+    pair_kernel = n_pad >= 64
     roofline = {
-        "bound": "fp32", "kernel": "render_paths<8,true,true> (packed FFMA2 intersection loop)",
+        "bound": "fp32",
+        "kernel": ("render_pairs<8,true> (two rays per thread: fused f32x2 filter over all spheres + reference arithmetic on the candidates)"
+                   if pair_kernel else "render_paths<8,true,true> (packed FFMA2 intersection loop)"),
         "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
         "peak_source": f"{info0['sm_count']} SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); "
                        "no tensor-core or HBM roof applies: the loop has no dense contraction and its scene is shared-memory resident",
         "algorithmic_flop_per_test": FLOP_PER_TEST, "tests_per_launch": rays_per_launch * n_pad,
-        "issue_bound_note": "15 of the 20 flops' instructions are mandatory separate roundings (parity), so 15 FP32 issue cycles/test "
-                            "is the hard floor: frac <= 20/30 = 0.667; see DESIGN.md",
+        "executed_flop_per_test": 14 if pair_kernel else 20,
+        "issue_cycles_per_32_tests": (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 32) / (rays_per_launch * n_pad / (kms * 1e-3)),
+        "issue_bound_note": ("achieved counts the reference's 20 flop per ray-sphere test (SURVEY 8d).  The filter scan executes 7 FMA "
+                             "(14 flop) per test; a packed FFMA2 holds the issue port 2 cycles, so its floor is 7 + 2 = 9 issue cycles "
+                             "per 32 tests (LDS.128 + 2 FSETP + 1 LOP3 per sphere per 64 rays); see DESIGN.md 5.2-5.3"
+                             if pair_kernel else
+                             "15 of the 20 flops' instructions are mandatory separate roundings (parity), so 15 FP32 issue cycles/test "
+                             "is the hard floor: frac <= 20/30 = 0.667; see DESIGN.md"),
         "kernel_ms": kms,
         "traffic": None, "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
     }

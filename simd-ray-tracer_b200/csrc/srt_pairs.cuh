@@ -20,7 +20,7 @@
 //   where R_i = r2_i (1 + 128u) + 128u |C_i|^2 is the sphere's squared radius inflated on the
 //   host (in double) and oo' = |O|^2 (1 - 160u) is deflated per ray, u = 2^-24.  DESIGN.md
 //   section 5.3 bounds every rounding of both evaluation orders and shows that the
-//   reference's `d2 < r2` (SIMD) or `!(d2 > r2)` (scalar) implies z > oo' with a 1.5x safety
+//   reference's `d2 < r2` (SIMD) or `!(d2 > r2)` (scalar) implies z > oo' with a 1.8x safety
 //   factor: the scan never loses a hit, it only admits a few near misses.
 //   `srt_filter_audit` (tests/test_gpu_filter.py) checks that superset property exhaustively
 //   on the GPU for every (ray, sphere) pair of whole renders.
