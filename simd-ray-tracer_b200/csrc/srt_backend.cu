@@ -9,6 +9,7 @@
 #include "srt_packed.cuh"
 #include "srt_pairs.cuh"
 #include "srt_path.cuh"
+#include "srt_pool.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -206,7 +207,7 @@ render_pairs(const __grid_constant__ KernelParams P) {
                     f3 o = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin), d = mk3(0.0f, 0.0f, 0.0f);   // out of work: parked
                     if (!(flags & kFlagDone)) {
                         uint64_t rng;
-                        primary_ray(P, pxy & 0xFFFFu, pxy >> 16, pix, k, rng, o, d);
+                        primary_ray<true>(P, pxy & 0xFFFFu, pxy >> 16, pix, k, rng, o, d);
                         SRT_ST(S_AX, r) = 1.0f; SRT_ST(S_AY, r) = 1.0f; SRT_ST(S_AZ, r) = 1.0f;
                         SRT_ST(S_LX, r) = 0.0f; SRT_ST(S_LY, r) = 0.0f; SRT_ST(S_LZ, r) = 0.0f;
                         SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
@@ -251,7 +252,7 @@ render_pairs(const __grid_constant__ KernelParams P) {
             }
             float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
             if (h.hit) s = s_scan[h.prim];                                    // centre only; .w is not used by shading
-            if (shade_scatter(P, h, s, o, d, atten, out, rng, bounce)) {
+            if (shade_scatter<true>(P, h, s, o, d, atten, out, rng, bounce)) {
                 const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, r), SRT_ST(S_MY, r), SRT_ST(S_MZ, r)), out, k);
                 SRT_ST(S_MX, r) = mean.x; SRT_ST(S_MY, r) = mean.y; SRT_ST(S_MZ, r) = mean.z;
                 SRT_SU(S_K, r) = k + P.sample_stride;
@@ -273,6 +274,205 @@ render_pairs(const __grid_constant__ KernelParams P) {
     // rays: one atomic per warp
     for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
     if (lane == 0 && rays) atomicAdd(P.rays, rays);
+}
+
+// ------------------------------------------------------------------------------------------
+// render_pool: render_pairs with the path slots owned by the CTA (srt_pool.cuh).  A warp pass
+// is either 64 PRIMARY rays (regenerate + 4-FFMA2 filter) or 64 SECONDARY rays (7-FFMA2 filter).
+// ------------------------------------------------------------------------------------------
+template <int W, bool FMA, int THREADS, int MINB, int SUB, int SUBP>
+__global__ void __launch_bounds__(THREADS, MINB)
+render_pool(const __grid_constant__ KernelParams P) {
+    constexpr uint32_t NS = 64u * (THREADS / 32 + 2);          // slots per CTA
+    constexpr uint32_t RCAP = NS <= 1024u ? 1024u : 2048u;     // ring capacity (power of two >= NS)
+    extern __shared__ float4 s_scan[];                         // {cx,cy,cz,-kappa}
+    float4 *const s_ptab = s_scan + P.n_pad;                   // {cx,cy,cz, 2C.O - kappa - oo'} for the camera origin
+    float *const s_r2 = reinterpret_cast<float *>(s_ptab + P.n_pad);
+    float *const st = s_r2 + P.n_pad;
+    uint32_t *const su = reinterpret_cast<uint32_t *>(st);
+    uint32_t *const ring0 = su + S_COUNT * NS;
+    uint32_t *const ring1 = ring0 + RCAP;
+    PoolCtl *const ctl = reinterpret_cast<PoolCtl *>(ring1 + RCAP);
+    const uint32_t tid = threadIdx.x;
+    const unsigned lane = tid & 31u;
+#define SRT_ST(f, id) st[(f) * NS + (id)]
+#define SRT_SU(f, id) su[(f) * NS + (id)]
+    const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
+    const f3 cam_o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+    {
+        // tables; the primary table in double: -(|C-O|^2 - R) - |O|^2 (1 - 160u), rounded once
+        const double u = 5.9604644775390625e-08;
+        const double ox = cam_o.x, oy = cam_o.y, oz = cam_o.z;
+        const double oo = (ox * ox + oy * oy + oz * oz) * (1.0 - 160.0 * u);
+        for (uint32_t i = tid; i < P.n_pad; i += THREADS) {
+            const float4 c = P.scan_table[i];
+            const float4 e = P.spheres[i];
+            s_scan[i] = c;
+            s_r2[i] = e.w;
+            float pw = -1.0e30f;
+            if (i < P.n_spheres) {
+                const double cx = c.x, cy = c.y, cz = c.z, r2 = e.w;
+                const double c2 = cx * cx + cy * cy + cz * cz;
+                const double R = r2 * (1.0 + 128.0 * u) + 128.0 * u * c2 + 1.0e-30;
+                pw = (float)(2.0 * (cx * ox + cy * oy + cz * oz) - (c2 - R) - oo);
+            }
+            s_ptab[i] = make_float4(c.x, c.y, c.z, pw);
+        }
+        for (uint32_t i = tid; i < NS; i += THREADS) {
+            SRT_SU(S_PIX, i) = kInvalidPixel;
+            SRT_SU(S_K, i) = k_end;
+            SRT_SU(S_FLAGS, i) = 0u;
+        }
+        for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? i : kRingEmpty; ring1[i] = kRingEmpty; }
+        if (tid == 0) {
+            ctl->head[0] = 0; ctl->tail[0] = NS; ctl->avail[0] = NS;
+            ctl->head[1] = 0; ctl->tail[1] = 0; ctl->avail[1] = 0;
+            ctl->inflight = 0; ctl->retired = 0; ctl->spins_steady = 0; ctl->spins_tail = 0;
+        }
+    }
+    __syncthreads();
+    unsigned long long rays = 0;
+
+    for (;;) {
+        uint32_t kind = 0, n = 0, pos = 0;
+        if (lane == 0) pool_acquire(ctl, NS, kind, n, pos);
+        kind = __shfl_sync(0xFFFFFFFFu, kind, 0);
+        n = __shfl_sync(0xFFFFFFFFu, n, 0);
+        pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
+        if (n == 0) break;
+        uint32_t *const ring = kind ? ring1 : ring0;
+        uint32_t id0 = lane < n ? pool_pop(ring, RCAP - 1u, pos + lane) : kRingEmpty;
+        uint32_t id1 = lane + 32u < n ? pool_pop(ring, RCAP - 1u, pos + 32u + lane) : kRingEmpty;
+        __threadfence_block();
+
+        f3 o0, o1, d0, d1;
+        Hit h0, h1;
+        CandQueue queue;
+        uint32_t qn;
+        pk2 ox, oy, oz, dx, dy, dz;
+        if (kind == 0) {
+            // ---- 64 slots that need a new primary ray: finish pixels, fetch new ones (A1) ----
+#pragma unroll 1
+            for (int r = 0; r < 2; ++r) {
+                const uint32_t s = r ? id1 : id0;
+                const bool valid = s != kRingEmpty;
+                uint32_t pix = kInvalidPixel, k = k_end, pxy = 0;
+                if (valid) { pix = SRT_SU(S_PIX, s); k = SRT_SU(S_K, s); pxy = SRT_SU(S_PXY, s); }
+                bool need = valid && (k == k_end);
+                if (need && pix != kInvalidPixel) {
+                    // A8 result + A9 tonemap/pack, main.cpp:484-492
+                    const float mx = SRT_ST(S_MX, s), my = SRT_ST(S_MY, s), mz = SRT_ST(S_MZ, s);
+                    P.accum[pix] = make_float4(mx, my, mz, 1.0f);
+                    if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mx, my, mz);
+                    pix = kInvalidPixel;
+                }
+                bool retire = false;
+                unsigned m = __ballot_sync(0xFFFFFFFFu, need);
+                while (m) {
+                    const unsigned leader = __ffs(m) - 1;
+                    unsigned base = 0;
+                    if (lane == leader) base = atomicAdd(P.work_counter, __popc(m));
+                    base = __shfl_sync(0xFFFFFFFFu, base, leader);
+                    if (need) {
+                        const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
+                        uint32_t px, py;
+                        if (item >= P.total_items) { retire = true; need = false; }
+                        else if (item_to_pixel(P, item, px, py)) {
+                            pix = py * P.width + px;
+                            pxy = px | (py << 16);
+                            k = P.first_sample;
+                            need = false;
+                            float4 prev = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1), zeroed arena
+                            if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) prev = P.accum[pix];
+                            SRT_ST(S_MX, s) = prev.x; SRT_ST(S_MY, s) = prev.y; SRT_ST(S_MZ, s) = prev.z;
+                        }
+                    }
+                    m = __ballot_sync(0xFFFFFFFFu, need);
+                }
+                const unsigned rm = __ballot_sync(0xFFFFFFFFu, retire);
+                if (rm && lane == (unsigned)(__ffs(rm) - 1)) atomicAdd(&ctl->retired, (unsigned)__popc(rm));
+                f3 o = cam_o, d = mk3(0.0f, 0.0f, 0.0f);
+                if (retire) { SRT_SU(S_PIX, s) = kInvalidPixel; if (r) id1 = kRingEmpty; else id0 = kRingEmpty; }
+                else if (valid) {
+                    uint64_t rng;
+                    primary_ray<true>(P, pxy & 0xFFFFu, pxy >> 16, pix, k, rng, o, d);
+                    SRT_ST(S_AX, s) = 1.0f; SRT_ST(S_AY, s) = 1.0f; SRT_ST(S_AZ, s) = 1.0f;
+                    SRT_ST(S_LX, s) = 0.0f; SRT_ST(S_LY, s) = 0.0f; SRT_ST(S_LZ, s) = 0.0f;
+                    SRT_SU(S_RNG_LO, s) = (uint32_t)rng; SRT_SU(S_RNG_HI, s) = (uint32_t)(rng >> 32);
+                    SRT_SU(S_PIX, s) = pix; SRT_SU(S_K, s) = k; SRT_SU(S_PXY, s) = pxy; SRT_SU(S_FLAGS, s) = 0u;   // bounce 0
+                }
+                if (r) { o1 = o; d1 = d; } else { o0 = o; d0 = d; }
+            }
+            ox = pk_make(cam_o.x, cam_o.x); oy = pk_make(cam_o.y, cam_o.y); oz = pk_make(cam_o.z, cam_o.z);
+            dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
+            qn = scan_primary<SUBP>(s_ptab, P.n_pad, cam_o.x, cam_o.y, cam_o.z, dx, dy, dz, queue);
+        } else {
+            // ---- 64 slots with a secondary ray ready ------------------------------------------
+            o0 = o1 = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin);
+            d0 = d1 = mk3(0.0f, 0.0f, 0.0f);
+            if (id0 != kRingEmpty) {
+                o0 = mk3(SRT_ST(S_OX, id0), SRT_ST(S_OY, id0), SRT_ST(S_OZ, id0));
+                d0 = mk3(SRT_ST(S_DX, id0), SRT_ST(S_DY, id0), SRT_ST(S_DZ, id0));
+            }
+            if (id1 != kRingEmpty) {
+                o1 = mk3(SRT_ST(S_OX, id1), SRT_ST(S_OY, id1), SRT_ST(S_OZ, id1));
+                d1 = mk3(SRT_ST(S_DX, id1), SRT_ST(S_DY, id1), SRT_ST(S_DZ, id1));
+            }
+            ox = pk_make(o0.x, o1.x); oy = pk_make(o0.y, o1.y); oz = pk_make(o0.z, o1.z);
+            dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
+            qn = scan_general<SUB>(s_scan, P.n_pad, ox, oy, oz, dx, dy, dz, queue);
+        }
+        select_candidates<W, FMA>(s_scan, s_r2, P.spheres, P.n_pad, P.n_spheres, queue, qn, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, h0, h1);
+
+        // ---- shade / scatter, one half after the other; push every slot to its next ring ------
+#pragma unroll 1
+        for (int r = 0; r < 2; ++r) {
+            const uint32_t s = r ? id1 : id0;
+            const bool valid = s != kRingEmpty;
+            bool ended = false;
+            if (valid) {
+                const Hit h = r ? h1 : h0;
+                f3 o = r ? o1 : o0, d = r ? d1 : d0;
+                rays += 1;                                                    // main.cpp:390
+                const uint32_t k = SRT_SU(S_K, s);
+                uint32_t bounce = SRT_SU(S_FLAGS, s) & kFlagBounceMask;
+                f3 atten = mk3(SRT_ST(S_AX, s), SRT_ST(S_AY, s), SRT_ST(S_AZ, s));
+                f3 out = mk3(SRT_ST(S_LX, s), SRT_ST(S_LY, s), SRT_ST(S_LZ, s));
+                uint64_t rng = (uint64_t)SRT_SU(S_RNG_LO, s) | ((uint64_t)SRT_SU(S_RNG_HI, s) << 32);
+                if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
+                    const uint32_t pix = SRT_SU(S_PIX, s);
+                    P.tap_t[pix] = h.t;
+                    P.tap_prim[pix] = h.prim;
+                }
+                float4 sp = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (h.hit) sp = s_scan[h.prim];                         // centre only; .w is not used by shading
+                ended = shade_scatter<true>(P, h, sp, o, d, atten, out, rng, bounce);
+                if (ended) {
+                    const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, s), SRT_ST(S_MY, s), SRT_ST(S_MZ, s)), out, k);
+                    SRT_ST(S_MX, s) = mean.x; SRT_ST(S_MY, s) = mean.y; SRT_ST(S_MZ, s) = mean.z;
+                    SRT_SU(S_K, s) = k + P.sample_stride;
+                } else {
+                    SRT_SU(S_RNG_LO, s) = (uint32_t)rng; SRT_SU(S_RNG_HI, s) = (uint32_t)(rng >> 32);
+                    SRT_ST(S_OX, s) = o.x; SRT_ST(S_OY, s) = o.y; SRT_ST(S_OZ, s) = o.z;
+                    SRT_ST(S_DX, s) = d.x; SRT_ST(S_DY, s) = d.y; SRT_ST(S_DZ, s) = d.z;
+                    SRT_ST(S_AX, s) = atten.x; SRT_ST(S_AY, s) = atten.y; SRT_ST(S_AZ, s) = atten.z;
+                    SRT_ST(S_LX, s) = out.x; SRT_ST(S_LY, s) = out.y; SRT_ST(S_LZ, s) = out.z;
+                    SRT_SU(S_FLAGS, s) = bounce;
+                }
+            }
+            pool_push(ctl, ring0, RCAP - 1u, 0, valid && ended, s, lane);
+            pool_push(ctl, ring1, RCAP - 1u, 1, valid && !ended, s, lane);
+        }
+        if (lane == 0) atomicSub(&ctl->inflight, 1u);
+    }
+#undef SRT_ST
+#undef SRT_SU
+
+    // rays: one atomic per warp
+    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
+    if (lane == 0 && rays) atomicAdd(P.rays, rays);
+    __syncthreads();
+    if (tid == 0 && P.debug) { atomicAdd(&P.debug[0], (unsigned long long)ctl->spins_steady); atomicAdd(&P.debug[1], (unsigned long long)ctl->spins_tail); }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -366,8 +566,9 @@ struct srt_backend {
     float4 *d_spheres2 = nullptr;        // sphere-pair layout (packed f32x2 kernels)
     float4 *d_scan = nullptr;            // filter table of the ray-pair kernel {cx,cy,cz,-kappa}
     DevMaterial *d_materials = nullptr;
-    int variant = 0;                     // 0: auto; 1: scalar-issue loop; 2..6: sphere-pair tuning; 7: force sphere-pair;
-                                         // 8: force ray-pair kernel (diagnostics, SRT_KERNEL_VARIANT)
+    int variant = 0;                     // 0: auto (pool kernel from 64 spheres, else sphere-pair); 1: scalar-issue loop;
+                                         // 2..6: sphere-pair tuning; 7: force sphere-pair; 8: force ray-pair kernel with
+                                         // thread-owned slots; 9: force pool kernel (diagnostics, SRT_KERNEL_VARIANT)
     uint32_t regen_threshold = 1;
     uint32_t n_spheres = 0, n_pad = 0;
     srt_scene_options opt = {0, 8, 1, 0};
@@ -426,22 +627,29 @@ constexpr int kPairThreads = 256;
 constexpr int kPairMinBlocks = 2;
 constexpr uint32_t kPairsMinSpheres = 64;
 struct PairConfig { int threads; render_kernel_t kernel; };
-static PairConfig pick_pairs_kernel(const srt_scene_options &o, int tuning) {
-    if (tuning > 0 && o.lane_width == 8 && o.fma_dot) {    // SRT_PAIR_CONFIG: occupancy experiments (W=8, FMA only)
-        switch (tuning) {
-            case 1: return {256, render_pairs<8, true, 256, 3>};
-            case 2: return {512, render_pairs<8, true, 512, 1>};
-            case 3: return {512, render_pairs<8, true, 512, 2>};
-            case 4: return {128, render_pairs<8, true, 128, 4>};
-            case 5: return {128, render_pairs<8, true, 128, 6>};
-            case 6: return {128, render_pairs<8, true, 128, 8>};
-            case 7: return {256, render_pairs<8, true, 256, 4>};
-            default: break;
-        }
-    }
+static PairConfig pick_pairs_kernel(const srt_scene_options &o) {
     if (o.lane_width == 1) return {kPairThreads, render_pairs<1, false, kPairThreads, kPairMinBlocks>};
     if (o.lane_width == 4) return {kPairThreads, o.fma_dot ? render_pairs<4, true, kPairThreads, kPairMinBlocks> : render_pairs<4, false, kPairThreads, kPairMinBlocks>};
     return {kPairThreads, o.fma_dot ? render_pairs<8, true, kPairThreads, kPairMinBlocks> : render_pairs<8, false, kPairThreads, kPairMinBlocks>};
+}
+// Pool kernel (srt_pool.cuh): CTA-owned path slots, primary / secondary warp passes.
+constexpr int kPoolThreads = 256;
+constexpr int kPoolMinBlocks = 2;
+// Unroll of the secondary-ray scan: 32 spheres per loop body is 3 % faster on >= 768 spheres, 16
+// is 4-9 % faster below (the bodies share the 6 KB L0 / 32 KB L1.5 instruction caches with the
+// primary scan, select and shade code).  Measured on B200, profiles/r1d_pool_tuning.log.
+template <int SUB>
+static render_kernel_t pick_pool_kernel_sub(const srt_scene_options &o) {
+    if (o.lane_width == 1) return render_pool<1, false, kPoolThreads, kPoolMinBlocks, SUB, 32>;
+    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, kPoolThreads, kPoolMinBlocks, SUB, 32> : render_pool<4, false, kPoolThreads, kPoolMinBlocks, SUB, 32>;
+    return o.fma_dot ? render_pool<8, true, kPoolThreads, kPoolMinBlocks, SUB, 32> : render_pool<8, false, kPoolThreads, kPoolMinBlocks, SUB, 32>;
+}
+static render_kernel_t pick_pool_kernel(const srt_scene_options &o, uint32_t n_pad) {
+    return n_pad >= 768 ? pick_pool_kernel_sub<32>(o) : pick_pool_kernel_sub<16>(o);
+}
+static size_t pool_smem_bytes(uint32_t n_pad, int threads) {
+    const size_t ns = 64u * (threads / 32 + 2), rcap = ns <= 1024 ? 1024 : 2048;
+    return (size_t)n_pad * (2 * sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + sizeof(PoolCtl);
 }
 static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
     return (size_t)n_pad * (sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * 2 * threads * sizeof(float);
@@ -474,8 +682,8 @@ int srt_create(srt_backend **out, int device_id) {
     SRT_CUDA(b, cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
     SRT_CUDA(b, cudaEventCreate(&b->ev_start));
     SRT_CUDA(b, cudaEventCreate(&b->ev_stop));
-    SRT_CUDA(b, cudaMalloc(&b->d_counters, 16));
-    SRT_CUDA(b, cudaMemset(b->d_counters, 0, 16));
+    SRT_CUDA(b, cudaMalloc(&b->d_counters, 64));
+    SRT_CUDA(b, cudaMemset(b->d_counters, 0, 64));
     SRT_CUDA(b, cudaMallocHost(&b->h_rays, sizeof(unsigned long long)));
     *b->h_rays = 0;
     return SRT_OK;
@@ -660,6 +868,7 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.rgba = b->d_rgba;
     P.rays = (unsigned long long *)b->d_counters;
     P.work_counter = (unsigned int *)(b->d_counters + 8);
+    P.debug = (unsigned long long *)(b->d_counters + 16);
     return SRT_OK;
 }
 
@@ -672,13 +881,14 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     rc = drain(b);
     if (rc) return rc;
 
-    int pair_tuning = 0;
-    if (const char *t = getenv("SRT_PAIR_CONFIG")) pair_tuning = atoi(t);
-    const PairConfig pc = pick_pairs_kernel(b->opt, pair_tuning);
+    const PairConfig pc = pick_pairs_kernel(b->opt);
     const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad, pc.threads) <= b->max_smem_optin;
-    const bool pairs = pairs_fit && (b->variant == 8 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
+    const bool pool_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, kPoolThreads) <= b->max_smem_optin;
+    const bool pool = pool_fit && (b->variant == 9 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
+    const bool pairs = !pool && pairs_fit && b->variant == 8;
     if (b->variant == 8 && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
-    const bool packed = !pairs && (b->variant != 1) && b->opt.lane_width != 1;
+    if (b->variant == 9 && !pool_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the pool kernel");
+    const bool packed = !pool && !pairs && (b->variant != 1) && b->opt.lane_width != 1;
     if (packed) P.spheres = b->d_spheres2;
     if (args->record_primary) {
         const size_t n = (size_t)b->width * b->height;
@@ -691,19 +901,19 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         b->tap_valid = true;
     }
 
-    render_kernel_t kernel = pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
-    const int threads = pairs ? pc.threads : kBlockThreads;
-    const size_t smem = pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
+    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, b->n_pad) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
+    const int threads = pool ? kPoolThreads : pairs ? pc.threads : kBlockThreads;
+    const size_t smem = pool ? pool_smem_bytes(b->n_pad, kPoolThreads) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
     if (per_sm < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
     uint32_t grid = (uint32_t)(b->sm_count * per_sm);                 // persistent: one resident wave
-    const uint32_t paths_per_block = (uint32_t)threads * (pairs ? 2u : 1u);
+    const uint32_t paths_per_block = pool ? 64u * (threads / 32 + 2) : (uint32_t)threads * (pairs ? 2u : 1u);
     const uint32_t max_useful = (P.total_items + paths_per_block - 1) / paths_per_block;
     if (grid > max_useful) grid = max_useful;
 
-    SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 16, b->stream));
+    SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 64, b->stream));
     SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
     kernel<<<grid, threads, smem, b->stream>>>(P);
     SRT_CUDA(b, cudaGetLastError());
@@ -711,6 +921,12 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     SRT_CUDA(b, cudaMemcpyAsync(b->h_rays, b->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, b->stream));
     b->launches += 1;
     b->in_flight = true;
+    if (getenv("SRT_POOL_DEBUG")) {
+        unsigned long long dbg[2] = {0, 0};
+        cudaStreamSynchronize(b->stream);
+        cudaMemcpy(dbg, b->d_counters + 16, sizeof(dbg), cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[srt pool] acquire spins: steady %llu, tail %llu\n", dbg[0], dbg[1]);
+    }
     return SRT_OK;
 }
 

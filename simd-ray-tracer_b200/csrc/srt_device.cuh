@@ -38,6 +38,13 @@ __device__ __forceinline__ f3 normalize3(f3 a) {
     return mk3(__fdiv_rn(a.x, len), __fdiv_rn(a.y, len), __fdiv_rn(a.z, len));
 }
 
+// Out-of-line copy: normalize3 is ~1 KB of SASS (3 IEEE divisions + sqrt) and a path step uses
+// it 6 times.  The pair / pool kernels call this one to stay closer to the 32 KB L1.5
+// instruction cache; the one-path kernel for tiny, shading-bound scenes keeps it inline.
+__device__ __noinline__ f3 normalize3_call(f3 a) { return normalize3(a); }
+template <bool OUTLINE>
+__device__ __forceinline__ f3 normalize3_sel(f3 a) { return OUTLINE ? normalize3_call(a) : normalize3(a); }
+
 // ---- PRNG: u32_random_state::PCG base.h:954-963, RandomFloat base.h:983-989 ------------
 // InverseMaxInt = (f32)((f64)(Max-Min)/4294967295.0) is exactly 2^-32 for a unit range and
 // 2^-31 for a range of 2 (checked on the host in tests/test_host_logic.py).
@@ -128,6 +135,7 @@ struct KernelParams {
     float *tap_t;                // optional
     unsigned long long *rays;
     unsigned int *work_counter;
+    unsigned long long *debug;   // optional diagnostics (pool kernel)
     uint32_t regen_threshold;    // start new paths once this many lanes of a warp are idle
     float neg_one, one;          // -1.0f / +1.0f, deliberately opaque to the compiler (srt_packed.cuh)
 };

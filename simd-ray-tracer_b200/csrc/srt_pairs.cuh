@@ -119,51 +119,114 @@ __device__ __forceinline__ void filter_sphere(uint32_t &mask, uint32_t bit, cons
     filter_mark(mask, za, ooa, zb, oob, bit);
 }
 
-// Scan + select for the two rays of a thread.
-//   scan       : shared memory, n_pad x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
+typedef uint2 CandQueue[kPairsMaxWords];   // {candidate mask, first sphere} of the 32-sphere chunks with candidates
+
+// Scan of the two rays of a thread over ALL spheres: fused arithmetic, branch-free.
+//   scan : shared memory, n_pad x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
+// Builds one 32-bit candidate mask per chunk of 32 spheres (bit 31 - j = sphere j of the chunk)
+// and appends the non-empty ones to a per-thread queue.  The queue lives in LOCAL memory on
+// purpose: ptxas cannot prove that a shared-memory store does not alias the sphere tables and
+// would serialise the next LDS.128 behind it.  One predicated STL.64 per chunk.
+// A parked slot must hold O = kIdleOrigin, D = 0 so that it never produces candidates.
+// SUB = spheres per unrolled loop body (8, 16 or 32): two scan loops, select and shade code share
+// the SM's instruction caches, so the bodies are kept at 16 spheres (~3 KB of SASS each).
+template <int SUB = 16>
+__device__ __forceinline__ uint32_t scan_general(const float4 *__restrict__ scan, uint32_t n_pad,
+                                                 pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, CandQueue &queue) {
+    uint32_t qn = 0;
+    float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
+    pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
+    pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
+    const FilterRay fa = filter_ray(oxa, oya, oza, dxa, dya, dza), fb = filter_ray(oxb, oyb, ozb, dxb, dyb, dzb);
+    const pk2 p2ox = pk_make(fa.p2ox, fb.p2ox), p2oy = pk_make(fa.p2oy, fb.p2oy), p2oz = pk_make(fa.p2oz, fb.p2oz);
+    const pk2 fdx = pk_make(fa.dx, fb.dx), fdy = pk_make(fa.dy, fb.dy), fdz = pk_make(fa.dz, fb.dz);
+    const pk2 od = pk_make(fa.od, fb.od);
+    const uint32_t full = n_pad >> 5;
+#pragma unroll 1
+    for (uint32_t c = 0; c < full; ++c) {
+        uint32_t mask = 0;
+#pragma unroll 1
+        for (int sub = 0; sub < 32 / SUB; ++sub) {
+            const float4 *blk = scan + (c << 5) + sub * SUB;
+            uint32_t m = 0;
+#pragma unroll
+            for (int j = 0; j < SUB; ++j) filter_sphere(m, (1u << (SUB - 1)) >> j, blk[j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
+            mask = SUB == 32 ? m : ((mask << (SUB & 31)) | m);
+        }
+        if (mask) { queue[qn] = make_uint2(mask, c << 5); qn += 1; }
+    }
+    if (n_pad & 31u) {                       // tail: 1..3 blocks of 8
+        uint32_t mask = 0, cnt = 0;
+#pragma unroll 1
+        for (uint32_t base = full << 5; base < n_pad; base += 8, cnt += 8) {
+            uint32_t m = 0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) filter_sphere(m, 0x80u >> j, scan[base + j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
+            mask = (mask << 8) | m;
+        }
+        mask <<= (32u - cnt);                // cnt in {8,16,24}: first tail sphere -> bit 31
+        if (mask) { queue[qn] = make_uint2(mask, full << 5); qn += 1; }
+    }
+    return qn;
+}
+
+// Scan for PRIMARY rays: every ray of the launch starts at the camera position O, so
+// 2 C.O - kappa - oo' is a per-sphere constant (`ptab[i].w`, evaluated in double when the CTA
+// starts) and the candidate test becomes  z = tt^2 + ptab.w > 0 :
+// 4 FFMA2 + LDS.128 + LOP3 + SHF per sphere per 64 rays (the sign bits of the two halves are
+// AND-ed and shifted into the mask; the mask is inverted per chunk).
+__device__ __forceinline__ void primary_sphere(uint32_t &nmask, const float4 s, pk2 dx, pk2 dy, pk2 dz, pk2 od) {
+    const pk2 cx = pk_make(s.x, s.x), cy = pk_make(s.y, s.y), cz = pk_make(s.z, s.z);
+    const pk2 tt = pk_fma(cx, dx, pk_fma(cy, dy, pk_fma(cz, dz, od)));
+    const pk2 z = pk_fma(tt, tt, pk_make(s.w, s.w));
+    float za, zb;
+    pk_split(z, za, zb);
+    nmask = __funnelshift_l(__float_as_uint(za) & __float_as_uint(zb), nmask, 1);   // 1 = both rays miss for sure
+}
+template <int SUB = 16>
+__device__ __forceinline__ uint32_t scan_primary(const float4 *__restrict__ ptab, uint32_t n_pad, float ox, float oy, float oz,
+                                                 pk2 dx, pk2 dy, pk2 dz, CandQueue &queue) {
+    uint32_t qn = 0;
+    float dxa, dxb, dya, dyb, dza, dzb;
+    pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
+    const FilterRay fa = filter_ray(ox, oy, oz, dxa, dya, dza), fb = filter_ray(ox, oy, oz, dxb, dyb, dzb);
+    const pk2 fdx = pk_make(fa.dx, fb.dx), fdy = pk_make(fa.dy, fb.dy), fdz = pk_make(fa.dz, fb.dz);
+    const pk2 od = pk_make(fa.od, fb.od);
+    const uint32_t full = n_pad >> 5;
+#pragma unroll 1
+    for (uint32_t c = 0; c < full; ++c) {
+        uint32_t nmask = 0;
+#pragma unroll 1
+        for (int sub = 0; sub < 32 / SUB; ++sub) {
+            const float4 *blk = ptab + (c << 5) + sub * SUB;
+#pragma unroll
+            for (int j = 0; j < SUB; ++j) primary_sphere(nmask, blk[j], fdx, fdy, fdz, od);
+        }
+        if (~nmask) { queue[qn] = make_uint2(~nmask, c << 5); qn += 1; }
+    }
+    if (n_pad & 31u) {
+        uint32_t nmask = 0, cnt = 0;
+#pragma unroll 1
+        for (uint32_t base = full << 5; base < n_pad; base += 8, cnt += 8) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) primary_sphere(nmask, ptab[base + j], fdx, fdy, fdz, od);
+        }
+        const uint32_t mask = (~nmask) << (32u - cnt);          // cnt in {8,16,24}: first tail sphere -> bit 31
+        if (mask) { queue[qn] = make_uint2(mask, full << 5); qn += 1; }
+    }
+    return qn;
+}
+
+// Select: the reference's arithmetic on the queued candidates, in index order.
+//   scan       : shared memory {cx, cy, cz, *} (centres)
 //   r2tab      : shared memory, n_pad x r2 (the reference's R*R, main.cpp:406; padding zero)
 //   sph_global : global memory, n_pad x {cx, cy, cz, r2}, only read by the rare replay_inside
-//   o*/d*: packed {slot0, slot1} origins and directions
-// The scan builds one 32-bit candidate mask per chunk of 32 spheres (bit 31 - j = sphere j of
-// the chunk) and appends the non-empty ones to a per-thread queue.  The queue lives in LOCAL
-// memory on purpose: ptxas cannot prove that a shared-memory store does not alias the sphere
-// tables and would serialise the next LDS.128 behind it.  One predicated STL.64 per chunk.
 template <int W, bool FMA>
-__device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
-                                               const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
-                                               pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
-                                               float neg_one_f, float one_f, Hit &h0, Hit &h1) {
-    uint2 queue[kPairsMaxWords];      // {candidate mask, first sphere} of the 32-sphere chunks that have candidates
-    uint32_t qn = 0;
-    {
-        // ---- scan: every sphere, both rays, fused arithmetic, branch-free --------------------
-        float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
-        pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
-        pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
-        const FilterRay fa = filter_ray(oxa, oya, oza, dxa, dya, dza), fb = filter_ray(oxb, oyb, ozb, dxb, dyb, dzb);
-        const pk2 p2ox = pk_make(fa.p2ox, fb.p2ox), p2oy = pk_make(fa.p2oy, fb.p2oy), p2oz = pk_make(fa.p2oz, fb.p2oz);
-        const pk2 fdx = pk_make(fa.dx, fb.dx), fdy = pk_make(fa.dy, fb.dy), fdz = pk_make(fa.dz, fb.dz);
-        const pk2 od = pk_make(fa.od, fb.od);
-        const uint32_t full = n_pad >> 5;
-#pragma unroll 1
-        for (uint32_t c = 0; c < full; ++c) {
-            uint32_t mask = 0;
-            const float4 *blk = scan + (c << 5);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) filter_sphere(mask, 0x80000000u >> j, blk[j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
-            if (mask) { queue[qn] = make_uint2(mask, c << 5); qn += 1; }
-        }
-        if (n_pad & 31u) {                       // tail: 1..3 blocks of 8
-            uint32_t mask = 0;
-#pragma unroll 1
-            for (uint32_t base = full << 5; base < n_pad; base += 8) {
-                const uint32_t bit0 = 0x80000000u >> (base & 31u);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) filter_sphere(mask, bit0 >> j, scan[base + j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
-            }
-            if (mask) { queue[qn] = make_uint2(mask, full << 5); qn += 1; }
-        }
-    }
+__device__ __forceinline__ void select_candidates(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
+                                                  const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
+                                                  const CandQueue &queue, uint32_t qn,
+                                                  pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
+                                                  float neg_one_f, float one_f, Hit &h0, Hit &h1) {
     // ---- select: the reference's arithmetic on the candidates, in index order ----------------
     const pk2 neg_one = pk_make(neg_one_f, neg_one_f), one = pk_make(one_f, one_f);
     Best b0 = best_init(), b1 = best_init();
@@ -214,6 +277,17 @@ __device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, 
             if (amb1) h1.inside = replay_inside<W, FMA>(sph_global, n_pad, oxb, oyb, ozb, dxb, dyb, dzb) != 0;
         }
     }
+}
+
+// Scan + select (general rays) for the two rays of a thread.
+template <int W, bool FMA>
+__device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
+                                               const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
+                                               pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
+                                               float neg_one_f, float one_f, Hit &h0, Hit &h1) {
+    CandQueue queue;
+    const uint32_t qn = scan_general<32>(scan, n_pad, ox, oy, oz, dx, dy, dz, queue);
+    select_candidates<W, FMA>(scan, r2tab, sph_global, n_pad, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one_f, one_f, h0, h1);
 }
 
 } // namespace srt

@@ -21,6 +21,7 @@ __device__ __forceinline__ bool item_to_pixel(const KernelParams &P, uint32_t it
 
 // A1 primary ray, main.cpp:375-385.  Stream contract: the path (sample k,
 // pixel) owns the RNG stream scramble(stream_base + k*W*H + pix); jitter x is drawn first.
+template <bool OUTLINE = false>
 __device__ __forceinline__ void primary_ray(const KernelParams &P, uint32_t px, uint32_t py, uint32_t pix, uint32_t k,
                                             uint64_t &rng, f3 &o, f3 &d) {
     rng = stream_seed(P.stream_base + (uint64_t)k * ((uint64_t)P.width * P.height) + pix);
@@ -35,12 +36,13 @@ __device__ __forceinline__ void primary_ray(const KernelParams &P, uint32_t px, 
     const f3 fc = mk3(P.cam.film_center[0], P.cam.film_center[1], P.cam.film_center[2]);
     const f3 film_p = add3(add3(fc, scale3(ax, cam_x)), scale3(ay, cam_y));
     o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
-    d = normalize3(sub3(film_p, o));
+    d = normalize3_sel<OUTLINE>(sub3(film_p, o));
 }
 
 // A5 + A6 for one path segment whose closest hit is `h` (`s` = winner's {cx,cy,cz,r2}, read
 // by the caller from whatever layout its kernel keeps; ignored on a miss).  Updates the ray,
 // attenuation, radiance, RNG and bounce count; returns true when the path ends.
+template <bool OUTLINE = false>
 __device__ __forceinline__ bool shade_scatter(const KernelParams &P, const Hit &h, const float4 s, f3 &o, f3 &d,
                                               f3 &atten, f3 &out, uint64_t &rng, uint32_t &bounce) {
     if (!h.hit) {
@@ -63,16 +65,16 @@ __device__ __forceinline__ bool shade_scatter(const KernelParams &P, const Hit &
     const f3 sc = sub3(mk3(s.x, s.y, s.z), o);
     const f3 ip = scale3(h.t, d);
     o = add3(o, ip);
-    f3 n = normalize3(sub3(ip, sc));
+    f3 n = normalize3_sel<OUTLINE>(sub3(ip, sc));
     const f3 pure = sub3(d, scale3(__fmul_rn(2.0f, dot3(d, n)), n));   // :453
     if (h.inside) n = neg3(n);
     if (ei.w == 0.0f) {
         const float rx = rand_float(rng, kInvU32Range2, -1.0f);
         const float ry = rand_float(rng, kInvU32Range2, -1.0f);
         const float rz = rand_float(rng, kInvU32Range2, -1.0f);
-        const f3 r = normalize3(mk3(rx, ry, rz));                      // :461
+        const f3 r = normalize3_sel<OUTLINE>(mk3(rx, ry, rz));                      // :461
         const f3 rb = add3(n, r);
-        d = normalize3(add3(scale3(dv.x, rb), scale3(cs.w, pure)));    // :463-464
+        d = normalize3_sel<OUTLINE>(add3(scale3(dv.x, rb), scale3(cs.w, pure)));    // :463-464
     } else {
         const float eta = h.inside ? ei.w : dv.y;                      // :466
         const float cd = dot3(neg3(d), n);
@@ -82,7 +84,7 @@ __device__ __forceinline__ bool shade_scatter(const KernelParams &P, const Hit &
         const bool cant = __fmul_rn(eta, sn) > 1.0f;                   // :471
         const f3 perp = scale3(eta, add3(d, scale3(c, n)));            // :472
         const float kk = -__fsqrt_rn(fabsf(__fsub_rn(1.0f, dot3(perp, perp))));   // :473
-        const f3 refr = normalize3(add3(perp, scale3(kk, n)));         // :474
+        const f3 refr = normalize3_sel<OUTLINE>(add3(perp, scale3(kk, n)));         // :474
         bool reflect = cant;                                            // :476 (|| short-circuit)
         if (!cant) reflect = reflectance(c, eta) > rand_float(rng, kInvU32Range1, 0.0f);
         d = (reflect && !h.inside) ? pure : refr;

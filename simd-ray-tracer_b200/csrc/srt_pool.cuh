@@ -1,0 +1,97 @@
+// srt_pool.cuh -- CTA-level path pools for the ray-pair kernel (sm_100a).
+//
+// render_pairs binds two path slots to a thread, so every pass mixes primary rays (fresh
+// samples) with secondary rays.  Primary rays all start at the camera: their filter needs
+// 4 FFMA2 per sphere instead of 7 (scan_primary, srt_pairs.cuh) -- but only if a whole warp
+// pass consists of primaries.  Here the path slots therefore belong to the CTA, not to a
+// thread: two rings in shared memory hold the ids of the slots that need a NEW PRIMARY ray
+// (ring P) and of those with a SECONDARY ray ready (ring S), and a warp repeatedly takes 64
+// ids of one kind, runs regenerate / scan / select / shade on them (two per lane, packed in
+// the f32x2 halves) and pushes every slot back to the ring its next step needs
+// (warp-aggregated, ballot + popc).  A slot still owns its pixel for all samples of the
+// launch, one path in flight per pixel, so the running mean of main.cpp:484-489 keeps its
+// order and every buffer stays bit-identical.
+//
+// Ring protocol (multi-producer / multi-consumer, no CTA barrier after start-up):
+//   push: pos = atomicAdd(tail, n); wait until ring[pos+i] is EMPTY; write id; fence;
+//         atomicAdd(avail, n)
+//   take: CAS avail -= n (only if avail >= n); pos = atomicAdd(head, n); wait until
+//         ring[pos+i] != EMPTY; read id; write EMPTY
+// avail counts published ids, so [head, head+n) has always been reserved by producers that
+// are a few instructions away from writing it: both waits are short and cannot deadlock.
+// With kPoolSlots = 64 * (warps + 2) one of the rings always holds a full batch while the
+// other warps are busy.
+#pragma once
+#include "srt_pairs.cuh"
+#include "srt_path.cuh"
+
+namespace srt {
+
+constexpr uint32_t kRingEmpty = 0xFFFFFFFFu;
+
+struct PoolCtl {
+    unsigned int head[2], tail[2], avail[2];   // ring 0 = P (needs a primary ray), ring 1 = S (secondary ready)
+    unsigned int inflight;                     // warps currently holding a batch
+    unsigned int retired;                      // slots that ran out of work
+    unsigned int spins_steady, spins_tail;     // diagnostics: acquire-loop iterations before / after work ran out
+};
+
+__device__ __forceinline__ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want_min, uint32_t &n, uint32_t &pos) {
+    unsigned int old = *(volatile unsigned int *)&ctl->avail[q];
+    while (old >= want_min && old > 0u) {
+        const unsigned int take = old < 64u ? old : 64u;
+        const unsigned int seen = atomicCAS(&ctl->avail[q], old, old - take);
+        if (seen == old) {
+            pos = atomicAdd(&ctl->head[q], take);
+            n = take;
+            atomicAdd(&ctl->inflight, 1u);
+            return true;
+        }
+        old = seen;
+    }
+    return false;
+}
+
+// Lane 0 decides; returns n == 0 when every slot of the CTA has retired.
+__device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, uint32_t &kind, uint32_t &n, uint32_t &pos) {
+    n = 0; kind = 0; pos = 0;
+    for (;;) {
+        if (pool_try_take(ctl, 0, 64u, n, pos)) { kind = 0; return; }
+        if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }
+        if (*(volatile unsigned int *)&ctl->inflight == 0u) {            // nobody will add to the rings: drain partial batches
+            if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
+            if (pool_try_take(ctl, 0, 1u, n, pos)) { kind = 0; return; }
+            if (*(volatile unsigned int *)&ctl->retired == n_slots) return;
+        }
+        if (*(volatile unsigned int *)&ctl->retired) ctl->spins_tail += 1; else ctl->spins_steady += 1;   // racy, diagnostic only
+        __nanosleep(100);
+    }
+}
+
+__device__ __forceinline__ uint32_t pool_pop(uint32_t *ring, uint32_t cap_mask, uint32_t pos) {
+    volatile uint32_t *e = ring + (pos & cap_mask);
+    uint32_t id;
+    while ((id = *e) == kRingEmpty) { }
+    *e = kRingEmpty;
+    return id;
+}
+
+// Warp-aggregated push of `id` by the lanes with `doit`.
+__device__ __forceinline__ void pool_push(PoolCtl *ctl, uint32_t *ring, uint32_t cap_mask, int q, bool doit, uint32_t id, unsigned lane) {
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, doit);
+    if (m == 0u) return;
+    const unsigned leader = __ffs(m) - 1;
+    unsigned pos = 0;
+    if (lane == leader) pos = atomicAdd(&ctl->tail[q], __popc(m));
+    pos = __shfl_sync(0xFFFFFFFFu, pos, leader);
+    if (doit) {
+        volatile uint32_t *e = ring + ((pos + __popc(m & ((1u << lane) - 1u))) & cap_mask);
+        while (*e != kRingEmpty) { }
+        *e = id;
+    }
+    __threadfence_block();
+    __syncwarp();
+    if (lane == leader) atomicAdd(&ctl->avail[q], __popc(m));
+}
+
+} // namespace srt

@@ -123,19 +123,43 @@ def test_filter_audit_tiny_far_spheres(backend, srt, oracle):
 
 @pytest.mark.parametrize("mode", MODES)
 def test_pair_kernel_equals_sphere_pair_kernel(backend, srt, monkeypatch, mode):
-    """1,024-sphere scene, 480x270, 4 spp, all bounces: the filter+select kernel and the kernel
-    that runs the reference's arithmetic on every sphere agree on every bit."""
+    """1,024-sphere scene, 480x270, 4 spp, all bounces: the production pool kernel (filter +
+    select, CTA-owned slots, primary / secondary passes), the ray-pair kernel with thread-owned
+    slots and the kernel that runs the reference's arithmetic on every sphere agree on every bit."""
     W, fma = mode
     spheres, sky, hdr = srt.host_scene(3)
     w, h = 480, 270
     cam = srt.host_camera(3, w, h, hdr)
     monkeypatch.setenv("SRT_KERNEL_VARIANT", "7")     # sphere-pair / scalar kernel, one path per thread
     ref = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
-    monkeypatch.setenv("SRT_KERNEL_VARIANT", "8")     # ray-pair kernel
-    new = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
+    monkeypatch.setenv("SRT_KERNEL_VARIANT", "8")     # ray-pair kernel, thread-owned slots
+    pairs = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
+    monkeypatch.setenv("SRT_KERNEL_VARIANT", "9")     # pool kernel (forced)
+    pool = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
     monkeypatch.delenv("SRT_KERNEL_VARIANT")
-    assert _same(ref, new) == {}
+    auto = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
+    assert _same(ref, pairs) == {}
+    assert _same(ref, pool) == {}
+    assert _same(ref, auto) == {}
     assert ref["rays"] > w * h * 4
+
+
+def test_pool_kernel_progressive_and_tiny_images(backend, srt, oracle):
+    """Pool kernel corner cases: fewer pixels than path slots (most slots retire at once),
+    progressive 1-spp launches that resume the accumulator, ragged sizes."""
+    spheres, sky, hdr = srt.host_scene(2)
+    for (w, h) in ((1, 1), (5, 3), (33, 17), (70, 9)):
+        cam = srt.host_camera(2, w, h, hdr)
+        o = oracle.render(spheres, sky, 8, 1, cam, w, h, 0, 3)
+        backend.set_scene(spheres, sky, 8, True)
+        backend.resize(w, h)
+        rays = 0
+        for k in range(3):
+            backend.render(cam, k, 1, record_primary=(k == 0))
+            rays += backend.wait()[1]
+        assert np.array_equal(backend.read_accum().view(np.uint32), o["accum"].view(np.uint32)), (w, h)
+        assert np.array_equal(backend.read_rgba8(), o["rgba"]), (w, h)
+        assert rays == o["rays"]
 
 
 @pytest.mark.parametrize("mode", [(8, 1), (4, 0), (1, 0), (8, 0), (4, 1)])
