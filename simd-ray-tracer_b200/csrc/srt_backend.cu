@@ -10,6 +10,7 @@
 #include "srt_pairs.cuh"
 #include "srt_path.cuh"
 #include "srt_pool.cuh"
+#include "srt_stream.cuh"
 
 #include <cstdio>
 #include <cstdlib>
@@ -280,43 +281,101 @@ render_pairs(const __grid_constant__ KernelParams P) {
 // render_pool: render_pairs with the path slots owned by the CTA (srt_pool.cuh).  A warp pass
 // is either 64 PRIMARY rays (regenerate + 4-FFMA2 filter) or 64 SECONDARY rays (7-FFMA2 filter).
 // ------------------------------------------------------------------------------------------
-template <int W, bool FMA, int THREADS, int MINB, int SUB, int SUBP>
+// ptab_value: the primary-ray filter constant of one sphere, in double, rounded once:
+// 2 C.O - kappa - oo' = -(|C-O|^2 - R) - |O|^2 (1 - 160u)   (srt_pairs.cuh)
+__device__ __forceinline__ float ptab_value(float4 c, float r2, double ox, double oy, double oz) {
+    const double u = 5.9604644775390625e-08;
+    const double cx = c.x, cy = c.y, cz = c.z;
+    const double c2 = cx * cx + cy * cy + cz * cz;
+    const double R = (double)r2 * (1.0 + 128.0 * u) + 128.0 * u * c2 + 1.0e-30;
+    const double oo = (ox * ox + oy * oy + oz * oz) * (1.0 - 160.0 * u);
+    return (float)(2.0 * (cx * ox + cy * oy + cz * oz) - (c2 - R) - oo);
+}
+// Streamed scenes: the primary table is built once per launch in global memory.
+__global__ void build_ptab_kernel(const float4 *scan, const float4 *spheres, float4 *ptab, uint32_t n_pad, uint32_t n_real,
+                                  float ox, float oy, float oz) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_pad) return;
+    const float4 c = scan[i];
+    ptab[i] = make_float4(c.x, c.y, c.z, i < n_real ? ptab_value(c, spheres[i].w, ox, oy, oz) : -1.0e30f);
+}
+
+// One pass of a warp over a streamed table (srt_stream.cuh): TMA bulk copies into the warp's
+// ring of stages, scan of each chunk, select after every kPairsMaxSpheres spheres.
+template <int SUB, int W, bool FMA, class Rays>
+__device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__restrict__ table, const float4 *__restrict__ spheres,
+                                            uint32_t n_pad, uint32_t n_real, const Rays &rays, unsigned lane,
+                                            pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, float neg_one, float one, Best &b0, Best &b1) {
+    const uint32_t n_chunks = (n_pad + kStreamChunk - 1) / kStreamChunk;
+    if (lane == 0) {
+        for (uint32_t c = 0; c < (uint32_t)kStreamStages && c < n_chunks; ++c) {
+            const uint32_t cnt = min((uint32_t)kStreamChunk, n_pad - c * kStreamChunk);
+            stream_issue(ws.stage + c * kStreamChunk, table + c * kStreamChunk, cnt * (uint32_t)sizeof(float4), ws.bar + c);
+        }
+    }
+    CandQueue queue;
+    uint32_t qn = 0;
+    const FetchGlobal fetch = {spheres};
+#pragma unroll 1
+    for (uint32_t c = 0; c < n_chunks; ++c) {
+        const uint32_t st = c % kStreamStages;
+        mbar_wait(ws.bar + st, (ws.parity >> st) & 1u);
+        ws.parity ^= 1u << st;
+        const uint32_t cnt = min((uint32_t)kStreamChunk, n_pad - c * kStreamChunk);
+        scan_tile<SUB>(ws.stage + st * kStreamChunk, cnt, c * kStreamChunk, rays, queue, qn);
+        __syncwarp();
+        const uint32_t nc = c + kStreamStages;
+        if (lane == 0 && nc < n_chunks) {
+            const uint32_t ncnt = min((uint32_t)kStreamChunk, n_pad - nc * kStreamChunk);
+            stream_issue(ws.stage + st * kStreamChunk, table + nc * kStreamChunk, ncnt * (uint32_t)sizeof(float4), ws.bar + st);
+        }
+        if (((c + 1) * kStreamChunk) % kPairsMaxSpheres == 0 || c + 1 == n_chunks) {
+            select_update<W, FMA>(fetch, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one, one, b0, b1);
+            qn = 0;
+        }
+    }
+}
+
+template <int W, bool FMA, int THREADS, int MINB, int SUB, int SUBP, bool STREAM>
 __global__ void __launch_bounds__(THREADS, MINB)
 render_pool(const __grid_constant__ KernelParams P) {
     constexpr uint32_t NS = 64u * (THREADS / 32 + 2);          // slots per CTA
     constexpr uint32_t RCAP = NS <= 1024u ? 1024u : 2048u;     // ring capacity (power of two >= NS)
-    extern __shared__ float4 s_scan[];                         // {cx,cy,cz,-kappa}
-    float4 *const s_ptab = s_scan + P.n_pad;                   // {cx,cy,cz, 2C.O - kappa - oo'} for the camera origin
-    float *const s_r2 = reinterpret_cast<float *>(s_ptab + P.n_pad);
-    float *const st = s_r2 + P.n_pad;
+    extern __shared__ float4 s_scan[];                         // resident: {cx,cy,cz,-kappa}
+    const uint32_t n_res = STREAM ? 0u : P.n_pad;              // spheres resident in shared memory
+    float4 *const s_ptab = s_scan + n_res;                     // resident: {cx,cy,cz, 2C.O - kappa - oo'} for the camera origin
+    float *const s_r2 = reinterpret_cast<float *>(s_ptab + n_res);
+    float *const st = s_r2 + n_res;
     uint32_t *const su = reinterpret_cast<uint32_t *>(st);
     uint32_t *const ring0 = su + S_COUNT * NS;
     uint32_t *const ring1 = ring0 + RCAP;
     PoolCtl *const ctl = reinterpret_cast<PoolCtl *>(ring1 + RCAP);
     const uint32_t tid = threadIdx.x;
     const unsigned lane = tid & 31u;
+    // streamed: per-warp TMA stages + barriers behind the control block (16-byte aligned)
+    WarpStream ws;
+    {
+        unsigned char *base = reinterpret_cast<unsigned char *>(ctl) + ((sizeof(PoolCtl) + 15u) & ~15u);
+        ws.stage = reinterpret_cast<float4 *>(base) + (tid >> 5) * (kStreamStages * kStreamChunk);
+        ws.bar = reinterpret_cast<uint64_t *>(base + (size_t)(THREADS / 32) * kStreamStages * kStreamChunk * sizeof(float4)) + (tid >> 5) * kStreamStages;
+        ws.parity = 0u;
+    }
 #define SRT_ST(f, id) st[(f) * NS + (id)]
 #define SRT_SU(f, id) su[(f) * NS + (id)]
     const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
     const f3 cam_o = mk3(P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
     {
-        // tables; the primary table in double: -(|C-O|^2 - R) - |O|^2 (1 - 160u), rounded once
-        const double u = 5.9604644775390625e-08;
-        const double ox = cam_o.x, oy = cam_o.y, oz = cam_o.z;
-        const double oo = (ox * ox + oy * oy + oz * oz) * (1.0 - 160.0 * u);
-        for (uint32_t i = tid; i < P.n_pad; i += THREADS) {
-            const float4 c = P.scan_table[i];
-            const float4 e = P.spheres[i];
-            s_scan[i] = c;
-            s_r2[i] = e.w;
-            float pw = -1.0e30f;
-            if (i < P.n_spheres) {
-                const double cx = c.x, cy = c.y, cz = c.z, r2 = e.w;
-                const double c2 = cx * cx + cy * cy + cz * cz;
-                const double R = r2 * (1.0 + 128.0 * u) + 128.0 * u * c2 + 1.0e-30;
-                pw = (float)(2.0 * (cx * ox + cy * oy + cz * oz) - (c2 - R) - oo);
+        if (!STREAM) {
+            for (uint32_t i = tid; i < P.n_pad; i += THREADS) {
+                const float4 c = P.scan_table[i];
+                const float r2 = P.spheres[i].w;
+                s_scan[i] = c;
+                s_r2[i] = r2;
+                s_ptab[i] = make_float4(c.x, c.y, c.z, i < P.n_spheres ? ptab_value(c, r2, cam_o.x, cam_o.y, cam_o.z) : -1.0e30f);
             }
-            s_ptab[i] = make_float4(c.x, c.y, c.z, pw);
+        } else if (lane == 0) {
+            for (int i = 0; i < kStreamStages; ++i) mbar_init(ws.bar + i, 1u);
+            mbar_fence_init();
         }
         for (uint32_t i = tid; i < NS; i += THREADS) {
             SRT_SU(S_PIX, i) = kInvalidPixel;
@@ -347,9 +406,10 @@ render_pool(const __grid_constant__ KernelParams P) {
 
         f3 o0, o1, d0, d1;
         Hit h0, h1;
-        CandQueue queue;
-        uint32_t qn;
+        Best b0 = best_init(), b1 = best_init();
         pk2 ox, oy, oz, dx, dy, dz;
+        CandQueue queue;                 // resident tables: one queue for either kind of pass
+        uint32_t qn = 0;
         if (kind == 0) {
             // ---- 64 slots that need a new primary ray: finish pixels, fetch new ones (A1) ----
 #pragma unroll 1
@@ -405,7 +465,12 @@ render_pool(const __grid_constant__ KernelParams P) {
             }
             ox = pk_make(cam_o.x, cam_o.x); oy = pk_make(cam_o.y, cam_o.y); oz = pk_make(cam_o.z, cam_o.z);
             dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
-            qn = scan_primary<SUBP>(s_ptab, P.n_pad, cam_o.x, cam_o.y, cam_o.z, dx, dy, dz, queue);
+            const ScanPrimary rays_p = make_scan_primary(cam_o.x, cam_o.y, cam_o.z, dx, dy, dz);
+            if (STREAM) {
+                stream_pass<SUBP, W, FMA>(ws, P.ptab, P.spheres, P.n_pad, P.n_spheres, rays_p, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+            } else {
+                scan_primary_tile<SUBP>(s_ptab, P.n_pad, 0u, rays_p, queue, qn);
+            }
         } else {
             // ---- 64 slots with a secondary ray ready ------------------------------------------
             o0 = o1 = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin);
@@ -420,9 +485,18 @@ render_pool(const __grid_constant__ KernelParams P) {
             }
             ox = pk_make(o0.x, o1.x); oy = pk_make(o0.y, o1.y); oz = pk_make(o0.z, o1.z);
             dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
-            qn = scan_general<SUB>(s_scan, P.n_pad, ox, oy, oz, dx, dy, dz, queue);
+            const ScanRays rays_s = make_scan_rays(ox, oy, oz, dx, dy, dz);
+            if (STREAM) {
+                stream_pass<SUB, W, FMA>(ws, P.scan_table, P.spheres, P.n_pad, P.n_spheres, rays_s, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+            } else {
+                scan_general_tile<SUB>(s_scan, P.n_pad, 0u, rays_s, queue, qn);
+            }
         }
-        select_candidates<W, FMA>(s_scan, s_r2, P.spheres, P.n_pad, P.n_spheres, queue, qn, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, h0, h1);
+        if (!STREAM) {
+            const FetchResident fetch = {s_scan, s_r2};
+            select_update<W, FMA>(fetch, P.n_spheres, queue, qn, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+        }
+        select_finish<W, FMA>(P.spheres, P.n_pad, b0, b1, ox, oy, oz, dx, dy, dz, h0, h1);
 
         // ---- shade / scatter, one half after the other; push every slot to its next ring ------
 #pragma unroll 1
@@ -445,7 +519,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                     P.tap_prim[pix] = h.prim;
                 }
                 float4 sp = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (h.hit) sp = s_scan[h.prim];                         // centre only; .w is not used by shading
+                if (h.hit) sp = STREAM ? __ldg(P.spheres + h.prim) : s_scan[h.prim];   // centre only; .w is not used by shading
                 ended = shade_scatter<true>(P, h, sp, o, d, atten, out, rng, bounce);
                 if (ended) {
                     const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, s), SRT_ST(S_MY, s), SRT_ST(S_MZ, s)), out, k);
@@ -565,10 +639,12 @@ struct srt_backend {
     float4 *d_spheres = nullptr;         // {cx,cy,cz,r2} per sphere (scalar-issue kernels)
     float4 *d_spheres2 = nullptr;        // sphere-pair layout (packed f32x2 kernels)
     float4 *d_scan = nullptr;            // filter table of the ray-pair kernel {cx,cy,cz,-kappa}
+    float4 *d_ptab = nullptr;            // primary-ray filter table of streamed scenes (rebuilt per launch)
     DevMaterial *d_materials = nullptr;
     int variant = 0;                     // 0: auto (pool kernel from 64 spheres, else sphere-pair); 1: scalar-issue loop;
                                          // 2..6: sphere-pair tuning; 7: force sphere-pair; 8: force ray-pair kernel with
-                                         // thread-owned slots; 9: force pool kernel (diagnostics, SRT_KERNEL_VARIANT)
+                                         // thread-owned slots; 9: force pool kernel; 12: force the STREAMED pool kernel
+                                         // (diagnostics, SRT_KERNEL_VARIANT)
     uint32_t regen_threshold = 1;
     uint32_t n_spheres = 0, n_pad = 0;
     srt_scene_options opt = {0, 8, 1, 0};
@@ -638,18 +714,22 @@ constexpr int kPoolMinBlocks = 2;
 // Unroll of the secondary-ray scan: 32 spheres per loop body is 3 % faster on >= 768 spheres, 16
 // is 4-9 % faster below (the bodies share the 6 KB L0 / 32 KB L1.5 instruction caches with the
 // primary scan, select and shade code).  Measured on B200, profiles/r1d_pool_tuning.log.
-template <int SUB>
+template <int SUB, bool STREAM>
 static render_kernel_t pick_pool_kernel_sub(const srt_scene_options &o) {
-    if (o.lane_width == 1) return render_pool<1, false, kPoolThreads, kPoolMinBlocks, SUB, 32>;
-    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, kPoolThreads, kPoolMinBlocks, SUB, 32> : render_pool<4, false, kPoolThreads, kPoolMinBlocks, SUB, 32>;
-    return o.fma_dot ? render_pool<8, true, kPoolThreads, kPoolMinBlocks, SUB, 32> : render_pool<8, false, kPoolThreads, kPoolMinBlocks, SUB, 32>;
+    if (o.lane_width == 1) return render_pool<1, false, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM>;
+    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM> : render_pool<4, false, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM>;
+    return o.fma_dot ? render_pool<8, true, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM> : render_pool<8, false, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM>;
 }
-static render_kernel_t pick_pool_kernel(const srt_scene_options &o, uint32_t n_pad) {
-    return n_pad >= 768 ? pick_pool_kernel_sub<32>(o) : pick_pool_kernel_sub<16>(o);
+static render_kernel_t pick_pool_kernel(const srt_scene_options &o, uint32_t n_pad, bool stream) {
+    if (stream) return pick_pool_kernel_sub<32, true>(o);
+    return n_pad >= 768 ? pick_pool_kernel_sub<32, false>(o) : pick_pool_kernel_sub<16, false>(o);
 }
-static size_t pool_smem_bytes(uint32_t n_pad, int threads) {
-    const size_t ns = 64u * (threads / 32 + 2), rcap = ns <= 1024 ? 1024 : 2048;
-    return (size_t)n_pad * (2 * sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + sizeof(PoolCtl);
+static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
+    const size_t ns = 64u * (threads / 32 + 2), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
+    size_t bytes = (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
+    if (stream) bytes += warps * kStreamStages * (kStreamChunk * sizeof(float4) + sizeof(uint64_t));
+    else bytes += (size_t)n_pad * (2 * sizeof(float4) + sizeof(float));
+    return bytes;
 }
 static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
     return (size_t)n_pad * (sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * 2 * threads * sizeof(float);
@@ -693,7 +773,7 @@ void srt_destroy(srt_backend *b) {
     if (!b) return;
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
-    cudaFree(b->d_spheres); cudaFree(b->d_spheres2); cudaFree(b->d_scan); cudaFree(b->d_materials);
+    cudaFree(b->d_spheres); cudaFree(b->d_spheres2); cudaFree(b->d_scan); cudaFree(b->d_ptab); cudaFree(b->d_materials);
     cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
     cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
     cudaFree(b->d_counters);
@@ -721,8 +801,7 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
     int rc = drain(b);
     if (rc) return rc;
     const uint32_t n_pad = (n_spheres + 7u) & ~7u;
-    if ((size_t)n_pad * sizeof(float4) > b->max_smem_optin)
-        return fail(b, SRT_ERR_TOO_LARGE, "srt_set_scene: scene exceeds the shared-memory resident limit");
+    if (n_spheres > (1u << 24)) return fail(b, SRT_ERR_TOO_LARGE, "srt_set_scene: more than 2^24 spheres");
     std::vector<float4> sph(n_pad, make_float4(0.f, 0.f, 0.f, 0.f));   // zero spheres: d2 < 0 never holds
     std::vector<DevMaterial> mats(n_pad);
     memset(mats.data(), 0, mats.size() * sizeof(DevMaterial));
@@ -757,10 +836,12 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
     }
     cudaFree(b->d_spheres); b->d_spheres = nullptr;
     cudaFree(b->d_scan); b->d_scan = nullptr;
+    cudaFree(b->d_ptab); b->d_ptab = nullptr;
     cudaFree(b->d_spheres2); b->d_spheres2 = nullptr;
     cudaFree(b->d_materials); b->d_materials = nullptr;
     SRT_CUDA(b, cudaMalloc(&b->d_spheres, sph.size() * sizeof(float4)));
     SRT_CUDA(b, cudaMalloc(&b->d_scan, scan.size() * sizeof(float4)));
+    SRT_CUDA(b, cudaMalloc(&b->d_ptab, scan.size() * sizeof(float4)));
     SRT_CUDA(b, cudaMemcpy(b->d_scan, scan.data(), scan.size() * sizeof(float4), cudaMemcpyHostToDevice));
     SRT_CUDA(b, cudaMalloc(&b->d_spheres2, sph2.size() * sizeof(float4)));
     SRT_CUDA(b, cudaMemcpy(b->d_spheres2, sph2.data(), sph2.size() * sizeof(float4), cudaMemcpyHostToDevice));
@@ -883,12 +964,17 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
 
     const PairConfig pc = pick_pairs_kernel(b->opt);
     const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad, pc.threads) <= b->max_smem_optin;
-    const bool pool_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, kPoolThreads) <= b->max_smem_optin;
-    const bool pool = pool_fit && (b->variant == 9 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres));
-    const bool pairs = !pool && pairs_fit && b->variant == 8;
-    if (b->variant == 8 && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
-    if (b->variant == 9 && !pool_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the pool kernel");
+    // kernel choice: tiny scenes -> one path per thread; otherwise the pool kernel, with the sphere
+    // tables resident in shared memory when they fit and streamed through per-warp TMA stages when not
+    const bool pool_res_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, kPoolThreads, false) <= b->max_smem_optin;
+    const bool want_pool = b->variant == 9 || b->variant == 12 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres);
+    const bool pool = want_pool;
+    const bool stream = pool && (b->variant == 12 || !pool_res_fit);
+    const bool pairs = !pool && b->variant == 8;
+    if (pairs && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
     const bool packed = !pool && !pairs && (b->variant != 1) && b->opt.lane_width != 1;
+    if (!pool && !pairs && (size_t)b->n_pad * sizeof(float4) > b->max_smem_optin)
+        return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the one-path kernel");
     if (packed) P.spheres = b->d_spheres2;
     if (args->record_primary) {
         const size_t n = (size_t)b->width * b->height;
@@ -901,9 +987,9 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         b->tap_valid = true;
     }
 
-    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, b->n_pad) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
+    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, b->n_pad, stream) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
     const int threads = pool ? kPoolThreads : pairs ? pc.threads : kBlockThreads;
-    const size_t smem = pool ? pool_smem_bytes(b->n_pad, kPoolThreads) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
+    const size_t smem = pool ? pool_smem_bytes(b->n_pad, kPoolThreads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
@@ -915,6 +1001,12 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
 
     SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 64, b->stream));
     SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
+    if (stream) {
+        P.ptab = b->d_ptab;
+        build_ptab_kernel<<<(b->n_pad + 255) / 256, 256, 0, b->stream>>>(b->d_scan, b->d_spheres, b->d_ptab, b->n_pad, b->n_spheres,
+                                                                        P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+        b->launches += 1;
+    }
     kernel<<<grid, threads, smem, b->stream>>>(P);
     SRT_CUDA(b, cudaGetLastError());
     SRT_CUDA(b, cudaEventRecord(b->ev_stop, b->stream));

@@ -119,6 +119,7 @@ struct KernelParams {
     const float4 *spheres;       // n_pad entries {cx,cy,cz,r2}, zero spheres as padding (never hit);
                                  // packed kernels: pair layout {x0,x1,y0,y1},{z0,z1,r2_0,r2_1}
     const float4 *scan_table;    // pair kernel: n_pad entries {cx,cy,cz,-kappa} (srt_pairs.cuh), padding -1e30
+    const float4 *ptab;          // streamed scenes: n_pad entries {cx,cy,cz, primary-ray filter constant}, built per launch
     const DevMaterial *materials;
     uint32_t n_pad;              // multiple of 8
     uint32_t n_spheres;          // real sphere count

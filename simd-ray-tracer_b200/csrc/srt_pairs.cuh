@@ -121,60 +121,80 @@ __device__ __forceinline__ void filter_sphere(uint32_t &mask, uint32_t bit, cons
 
 typedef uint2 CandQueue[kPairsMaxWords];   // {candidate mask, first sphere} of the 32-sphere chunks with candidates
 
-// Scan of the two rays of a thread over ALL spheres: fused arithmetic, branch-free.
-//   scan : shared memory, n_pad x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
-// Builds one 32-bit candidate mask per chunk of 32 spheres (bit 31 - j = sphere j of the chunk)
-// and appends the non-empty ones to a per-thread queue.  The queue lives in LOCAL memory on
-// purpose: ptxas cannot prove that a shared-memory store does not alias the sphere tables and
-// would serialise the next LDS.128 behind it.  One predicated STL.64 per chunk.
-// A parked slot must hold O = kIdleOrigin, D = 0 so that it never produces candidates.
-// SUB = spheres per unrolled loop body (8, 16 or 32): two scan loops, select and shade code share
-// the SM's instruction caches, so the bodies are kept at 16 spheres (~3 KB of SASS each).
-template <int SUB = 16>
-__device__ __forceinline__ uint32_t scan_general(const float4 *__restrict__ scan, uint32_t n_pad,
-                                                 pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, CandQueue &queue) {
-    uint32_t qn = 0;
+// ---- scan: every sphere, both rays of the thread, fused arithmetic, branch-free -----------------
+// A table (or a tile of it) is scanned in chunks of 32 spheres; each chunk yields a 32-bit
+// candidate mask (bit 31 - j = sphere j of the chunk) and the non-empty ones are appended to a
+// per-thread queue.  The queue lives in LOCAL memory on purpose: ptxas cannot prove that a
+// shared-memory store does not alias the sphere tables and would serialise the next LDS.128
+// behind it.  One predicated STL.64 per chunk.  `count` is a multiple of 8 and only the last
+// tile of a table may have count % 32 != 0; `first` is the table index of tile[0] (multiple of 32).
+// SUB = spheres per unrolled loop body (16 or 32): the loop bodies share the SM's 6 KB L0 / 32 KB
+// L1.5 instruction caches with the select and shade code.
+
+// Per-pass constants of a general ray pair.  A parked slot must hold O = kIdleOrigin, D = 0.
+struct ScanRays {
+    pk2 p2ox, p2oy, p2oz, dx, dy, dz, od;
+    float ooa, oob;
+};
+__device__ __forceinline__ ScanRays make_scan_rays(pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz) {
     float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
     pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
     pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
     const FilterRay fa = filter_ray(oxa, oya, oza, dxa, dya, dza), fb = filter_ray(oxb, oyb, ozb, dxb, dyb, dzb);
-    const pk2 p2ox = pk_make(fa.p2ox, fb.p2ox), p2oy = pk_make(fa.p2oy, fb.p2oy), p2oz = pk_make(fa.p2oz, fb.p2oz);
-    const pk2 fdx = pk_make(fa.dx, fb.dx), fdy = pk_make(fa.dy, fb.dy), fdz = pk_make(fa.dz, fb.dz);
-    const pk2 od = pk_make(fa.od, fb.od);
-    const uint32_t full = n_pad >> 5;
+    ScanRays r;
+    r.p2ox = pk_make(fa.p2ox, fb.p2ox); r.p2oy = pk_make(fa.p2oy, fb.p2oy); r.p2oz = pk_make(fa.p2oz, fb.p2oz);
+    r.dx = pk_make(fa.dx, fb.dx); r.dy = pk_make(fa.dy, fb.dy); r.dz = pk_make(fa.dz, fb.dz);
+    r.od = pk_make(fa.od, fb.od);
+    r.ooa = fa.oo; r.oob = fb.oo;
+    return r;
+}
+//   tile : shared memory, count x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
+template <int SUB>
+__device__ __forceinline__ void scan_general_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first,
+                                                  const ScanRays &r, CandQueue &queue, uint32_t &qn) {
+    const uint32_t full = count >> 5;
 #pragma unroll 1
     for (uint32_t c = 0; c < full; ++c) {
         uint32_t mask = 0;
 #pragma unroll 1
         for (int sub = 0; sub < 32 / SUB; ++sub) {
-            const float4 *blk = scan + (c << 5) + sub * SUB;
+            const float4 *blk = tile + (c << 5) + sub * SUB;
             uint32_t m = 0;
 #pragma unroll
-            for (int j = 0; j < SUB; ++j) filter_sphere(m, (1u << (SUB - 1)) >> j, blk[j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
+            for (int j = 0; j < SUB; ++j) filter_sphere(m, (1u << (SUB - 1)) >> j, blk[j], r.p2ox, r.p2oy, r.p2oz, r.dx, r.dy, r.dz, r.od, r.ooa, r.oob);
             mask = SUB == 32 ? m : ((mask << (SUB & 31)) | m);
         }
-        if (mask) { queue[qn] = make_uint2(mask, c << 5); qn += 1; }
+        if (mask) { queue[qn] = make_uint2(mask, first + (c << 5)); qn += 1; }
     }
-    if (n_pad & 31u) {                       // tail: 1..3 blocks of 8
+    if (count & 31u) {                       // tail: 1..3 blocks of 8
         uint32_t mask = 0, cnt = 0;
 #pragma unroll 1
-        for (uint32_t base = full << 5; base < n_pad; base += 8, cnt += 8) {
+        for (uint32_t base = full << 5; base < count; base += 8, cnt += 8) {
             uint32_t m = 0;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) filter_sphere(m, 0x80u >> j, scan[base + j], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, fa.oo, fb.oo);
+            for (int j = 0; j < 8; ++j) filter_sphere(m, 0x80u >> j, tile[base + j], r.p2ox, r.p2oy, r.p2oz, r.dx, r.dy, r.dz, r.od, r.ooa, r.oob);
             mask = (mask << 8) | m;
         }
         mask <<= (32u - cnt);                // cnt in {8,16,24}: first tail sphere -> bit 31
-        if (mask) { queue[qn] = make_uint2(mask, full << 5); qn += 1; }
+        if (mask) { queue[qn] = make_uint2(mask, first + (full << 5)); qn += 1; }
     }
-    return qn;
 }
 
-// Scan for PRIMARY rays: every ray of the launch starts at the camera position O, so
-// 2 C.O - kappa - oo' is a per-sphere constant (`ptab[i].w`, evaluated in double when the CTA
-// starts) and the candidate test becomes  z = tt^2 + ptab.w > 0 :
-// 4 FFMA2 + LDS.128 + LOP3 + SHF per sphere per 64 rays (the sign bits of the two halves are
-// AND-ed and shifted into the mask; the mask is inverted per chunk).
+// PRIMARY rays: every ray of the launch starts at the camera position O, so
+// 2 C.O - kappa - oo' is a per-sphere constant (`ptab[i].w`, evaluated in double per launch) and
+// the candidate test becomes  z = tt^2 + ptab.w > 0 :  4 FFMA2 + LDS.128 + LOP3 + SHF per sphere
+// per 64 rays (the sign bits of the two halves are AND-ed and shifted into the mask, which is
+// inverted per chunk).
+struct ScanPrimary { pk2 dx, dy, dz, od; };
+__device__ __forceinline__ ScanPrimary make_scan_primary(float ox, float oy, float oz, pk2 dx, pk2 dy, pk2 dz) {
+    float dxa, dxb, dya, dyb, dza, dzb;
+    pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
+    const FilterRay fa = filter_ray(ox, oy, oz, dxa, dya, dza), fb = filter_ray(ox, oy, oz, dxb, dyb, dzb);
+    ScanPrimary r;
+    r.dx = pk_make(fa.dx, fb.dx); r.dy = pk_make(fa.dy, fb.dy); r.dz = pk_make(fa.dz, fb.dz);
+    r.od = pk_make(fa.od, fb.od);
+    return r;
+}
 __device__ __forceinline__ void primary_sphere(uint32_t &nmask, const float4 s, pk2 dx, pk2 dy, pk2 dz, pk2 od) {
     const pk2 cx = pk_make(s.x, s.x), cy = pk_make(s.y, s.y), cz = pk_make(s.z, s.z);
     const pk2 tt = pk_fma(cx, dx, pk_fma(cy, dy, pk_fma(cz, dz, od)));
@@ -183,55 +203,63 @@ __device__ __forceinline__ void primary_sphere(uint32_t &nmask, const float4 s, 
     pk_split(z, za, zb);
     nmask = __funnelshift_l(__float_as_uint(za) & __float_as_uint(zb), nmask, 1);   // 1 = both rays miss for sure
 }
-template <int SUB = 16>
-__device__ __forceinline__ uint32_t scan_primary(const float4 *__restrict__ ptab, uint32_t n_pad, float ox, float oy, float oz,
-                                                 pk2 dx, pk2 dy, pk2 dz, CandQueue &queue) {
-    uint32_t qn = 0;
-    float dxa, dxb, dya, dyb, dza, dzb;
-    pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
-    const FilterRay fa = filter_ray(ox, oy, oz, dxa, dya, dza), fb = filter_ray(ox, oy, oz, dxb, dyb, dzb);
-    const pk2 fdx = pk_make(fa.dx, fb.dx), fdy = pk_make(fa.dy, fb.dy), fdz = pk_make(fa.dz, fb.dz);
-    const pk2 od = pk_make(fa.od, fb.od);
-    const uint32_t full = n_pad >> 5;
+template <int SUB>
+__device__ __forceinline__ void scan_primary_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first,
+                                                  const ScanPrimary &r, CandQueue &queue, uint32_t &qn) {
+    const uint32_t full = count >> 5;
 #pragma unroll 1
     for (uint32_t c = 0; c < full; ++c) {
         uint32_t nmask = 0;
 #pragma unroll 1
         for (int sub = 0; sub < 32 / SUB; ++sub) {
-            const float4 *blk = ptab + (c << 5) + sub * SUB;
+            const float4 *blk = tile + (c << 5) + sub * SUB;
 #pragma unroll
-            for (int j = 0; j < SUB; ++j) primary_sphere(nmask, blk[j], fdx, fdy, fdz, od);
+            for (int j = 0; j < SUB; ++j) primary_sphere(nmask, blk[j], r.dx, r.dy, r.dz, r.od);
         }
-        if (~nmask) { queue[qn] = make_uint2(~nmask, c << 5); qn += 1; }
+        if (~nmask) { queue[qn] = make_uint2(~nmask, first + (c << 5)); qn += 1; }
     }
-    if (n_pad & 31u) {
+    if (count & 31u) {
         uint32_t nmask = 0, cnt = 0;
 #pragma unroll 1
-        for (uint32_t base = full << 5; base < n_pad; base += 8, cnt += 8) {
+        for (uint32_t base = full << 5; base < count; base += 8, cnt += 8) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) primary_sphere(nmask, ptab[base + j], fdx, fdy, fdz, od);
+            for (int j = 0; j < 8; ++j) primary_sphere(nmask, tile[base + j], r.dx, r.dy, r.dz, r.od);
         }
         const uint32_t mask = (~nmask) << (32u - cnt);          // cnt in {8,16,24}: first tail sphere -> bit 31
-        if (mask) { queue[qn] = make_uint2(mask, full << 5); qn += 1; }
+        if (mask) { queue[qn] = make_uint2(mask, first + (full << 5)); qn += 1; }
     }
-    return qn;
 }
 
-// Select: the reference's arithmetic on the queued candidates, in index order.
-//   scan       : shared memory {cx, cy, cz, *} (centres)
-//   r2tab      : shared memory, n_pad x r2 (the reference's R*R, main.cpp:406; padding zero)
-//   sph_global : global memory, n_pad x {cx, cy, cz, r2}, only read by the rare replay_inside
-template <int W, bool FMA>
-__device__ __forceinline__ void select_candidates(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
-                                                  const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
-                                                  const CandQueue &queue, uint32_t qn,
-                                                  pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
-                                                  float neg_one_f, float one_f, Hit &h0, Hit &h1) {
-    // ---- select: the reference's arithmetic on the candidates, in index order ----------------
+// Overloads by ray-constant type, for code that is generic over the kind of pass.
+template <int SUB>
+__device__ __forceinline__ void scan_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first, const ScanRays &r, CandQueue &queue, uint32_t &qn) {
+    scan_general_tile<SUB>(tile, count, first, r, queue, qn);
+}
+template <int SUB>
+__device__ __forceinline__ void scan_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first, const ScanPrimary &r, CandQueue &queue, uint32_t &qn) {
+    scan_primary_tile<SUB>(tile, count, first, r, queue, qn);
+}
+
+// ---- select: the reference's arithmetic on the queued candidates, in index order ----------------
+// Sphere fetchers: {cx, cy, cz, r2} of sphere idx with the reference's operands.
+struct FetchResident {              // centres from the resident filter table, r2 = R*R (main.cpp:406) beside it
+    const float4 *scan;
+    const float *r2tab;
+    __device__ __forceinline__ float4 operator()(uint32_t idx) const { float4 s = scan[idx]; s.w = r2tab[idx]; return s; }
+};
+struct FetchGlobal {                // streamed scenes: straight from the {cx,cy,cz,r2} table in global memory (L2)
+    const float4 *sph;
+    __device__ __forceinline__ float4 operator()(uint32_t idx) const { return __ldg(sph + idx); }
+};
+
+// Folds the queue into the running closest-hit state of the two rays.  Flattened over the
+// thread's own candidates: the warp iterates max-over-lanes(candidates) times, not once per
+// chunk that has a candidate in any lane.
+template <int W, bool FMA, class Fetch>
+__device__ __forceinline__ void select_update(const Fetch &fetch, uint32_t n_real, const CandQueue &queue, uint32_t qn,
+                                              pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
+                                              float neg_one_f, float one_f, Best &b0, Best &b1) {
     const pk2 neg_one = pk_make(neg_one_f, neg_one_f), one = pk_make(one_f, one_f);
-    Best b0 = best_init(), b1 = best_init();
-    // Flattened over the thread's own candidates: the warp iterates max-over-lanes(candidates)
-    // times, not once per chunk that has a candidate in any lane.
     uint32_t qi = 0, m = 0, first = 0;
     for (;;) {
         if (m == 0) {
@@ -242,8 +270,7 @@ __device__ __forceinline__ void select_candidates(const float4 *__restrict__ sca
         const uint32_t j = (uint32_t)__clz((int)m);
         m &= ~(0x80000000u >> j);
         const uint32_t idx = first + j;
-        float4 s = scan[idx];
-        s.w = r2tab[idx];
+        const float4 s = fetch(idx);
         const pk2 scx = pk_sub(pk_make(s.x, s.x), ox);                         // main.cpp:401
         const pk2 scy = pk_sub(pk_make(s.y, s.y), oy);
         const pk2 scz = pk_sub(pk_make(s.z, s.z), oz);
@@ -264,6 +291,13 @@ __device__ __forceinline__ void select_candidates(const float4 *__restrict__ sca
             if (d2b < s.w) best_update<W>(b1, tb, d2b, s.w, idx);
         }
     }
+}
+
+// Closest-hit records from the final state; resolves the sticky-inside ambiguity.
+//   sph_global : global memory, n_pad x {cx, cy, cz, r2}, only read by the rare replay_inside
+template <int W, bool FMA>
+__device__ __forceinline__ void select_finish(const float4 *__restrict__ sph_global, uint32_t n_pad, const Best &b0, const Best &b1,
+                                              pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, Hit &h0, Hit &h1) {
     h0.t = b0.t; h0.hit = !(b0.t == kMax); h0.prim = h0.hit ? b0.idx : 0xFFFFFFFFu; h0.inside = b0.test != 0;
     h1.t = b1.t; h1.hit = !(b1.t == kMax); h1.prim = h1.hit ? b1.idx : 0xFFFFFFFFu; h1.inside = b1.test != 0;
     if (W != 1) {
@@ -279,15 +313,20 @@ __device__ __forceinline__ void select_candidates(const float4 *__restrict__ sca
     }
 }
 
-// Scan + select (general rays) for the two rays of a thread.
+// Scan + select (general rays, resident tables) for the two rays of a thread.
 template <int W, bool FMA>
 __device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
                                                const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
                                                pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
                                                float neg_one_f, float one_f, Hit &h0, Hit &h1) {
     CandQueue queue;
-    const uint32_t qn = scan_general<32>(scan, n_pad, ox, oy, oz, dx, dy, dz, queue);
-    select_candidates<W, FMA>(scan, r2tab, sph_global, n_pad, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one_f, one_f, h0, h1);
+    uint32_t qn = 0;
+    const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
+    scan_general_tile<32>(scan, n_pad, 0u, rays, queue, qn);
+    Best b0 = best_init(), b1 = best_init();
+    const FetchResident fetch = {scan, r2tab};
+    select_update<W, FMA>(fetch, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one_f, one_f, b0, b1);
+    select_finish<W, FMA>(sph_global, n_pad, b0, b1, ox, oy, oz, dx, dy, dz, h0, h1);
 }
 
 } // namespace srt

@@ -136,10 +136,13 @@ def test_pair_kernel_equals_sphere_pair_kernel(backend, srt, monkeypatch, mode):
     pairs = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
     monkeypatch.setenv("SRT_KERNEL_VARIANT", "9")     # pool kernel (forced)
     pool = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
+    monkeypatch.setenv("SRT_KERNEL_VARIANT", "12")    # pool kernel, tables streamed through per-warp TMA stages
+    streamed = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
     monkeypatch.delenv("SRT_KERNEL_VARIANT")
     auto = _render(backend, spheres, sky, W, fma, cam, w, h, 4)
     assert _same(ref, pairs) == {}
     assert _same(ref, pool) == {}
+    assert _same(ref, streamed) == {}
     assert _same(ref, auto) == {}
     assert ref["rays"] > w * h * 4
 
@@ -160,6 +163,38 @@ def test_pool_kernel_progressive_and_tiny_images(backend, srt, oracle):
         assert np.array_equal(backend.read_accum().view(np.uint32), o["accum"].view(np.uint32)), (w, h)
         assert np.array_equal(backend.read_rgba8(), o["rgba"]), (w, h)
         assert rays == o["rays"]
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_streamed_64k_scene_vs_oracle(backend, srt, oracle, mode):
+    """BASELINE configs[4]: 65,536 spheres (3 x 1 MiB of tables, not shared-memory resident):
+    the streamed pool kernel equals the CPU oracle bit for bit, and the filter audit is clean."""
+    W, fma = mode
+    spheres, sky, hdr = srt.host_scene(4)
+    assert len(spheres) > 65000
+    w, h = 64, 36
+    cam = srt.host_camera(4, w, h, hdr)
+    o = oracle.render(spheres, sky, W, fma, cam, w, h, 0, 1)
+    g = _render(backend, spheres, sky, W, fma, cam, w, h, 1)
+    assert _same(o, g) == {}
+    backend.set_scene(spheres, sky, W, bool(fma))
+    backend.resize(16, 9)
+    a = backend.filter_audit(srt.host_camera(4, 16, 9, hdr), 0, 1)
+    assert a["hits"] > 0 and a["violations"] == 0, a
+
+
+def test_streamed_ragged_scene_sizes(backend, srt, oracle, monkeypatch):
+    """Streaming corner cases: table sizes that are not multiples of the 64-sphere stage or of
+    the 32-sphere mask word (last chunk of 8, 16, 24, 40 ... spheres)."""
+    spheres, sky, hdr = srt.host_scene(2)
+    w, h = 48, 27
+    cam = srt.host_camera(2, w, h, hdr)
+    monkeypatch.setenv("SRT_KERNEL_VARIANT", "12")
+    for n in (65, 72, 100, 129, 200, 257, 482):
+        sp = spheres[:n]
+        o = oracle.render(sp, sky, 8, 1, cam, w, h, 0, 2)
+        g = _render(backend, sp, sky, 8, 1, cam, w, h, 2)
+        assert _same(o, g) == {}, n
 
 
 @pytest.mark.parametrize("mode", [(8, 1), (4, 0), (1, 0), (8, 0), (4, 1)])
