@@ -308,19 +308,25 @@ def run_gpu_arm(args):
     rays_per_launch = float(np.mean(kernel_rays))
     achieved = FLOP_PER_TEST * rays_per_launch * n_pad / (kms * 1e-3) / 1e12
     pair_kernel = n_pad >= 64
+    primary_per_launch = float(W * H * SPP) / max(1, n_gpus)   # one render launch per step per rank
     roofline = {
         "bound": "fp32",
-        "kernel": ("render_pairs<8,true> (two rays per thread: fused f32x2 filter over all spheres + reference arithmetic on the candidates)"
+        "kernel": ("render_pool<8,true> (CTA-owned path slots, warp passes of 64 primary or 64 secondary rays, two rays per thread: "
+                   "fused f32x2 filter over all spheres + reference arithmetic on the candidates"
+                   + ("; tables streamed through per-warp TMA stages)" if n_pad > 8192 else "; tables resident in shared memory)")
                    if pair_kernel else "render_paths<8,true,true> (packed FFMA2 intersection loop)"),
         "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
         "peak_source": f"{info0['sm_count']} SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); "
                        "no tensor-core or HBM roof applies: the loop has no dense contraction and its scene is shared-memory resident",
         "algorithmic_flop_per_test": FLOP_PER_TEST, "tests_per_launch": rays_per_launch * n_pad,
-        "executed_flop_per_test": 14 if pair_kernel else 20,
+        "executed_flop_per_test": "8 (primary rays: 4 FMA) / 14 (secondary rays: 7 FMA)" if pair_kernel else 20,
+        "frac_executed": ((8.0 * primary_per_launch + 14.0 * (rays_per_launch - primary_per_launch)) if pair_kernel
+                          else 20.0 * rays_per_launch) * n_pad / (kms * 1e-3) / 1e12 / peak_tflops,
         "issue_cycles_per_32_tests": (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 32) / (rays_per_launch * n_pad / (kms * 1e-3)),
         "issue_bound_note": ("achieved counts the reference's 20 flop per ray-sphere test (SURVEY 8d).  The filter scan executes 7 FMA "
-                             "(14 flop) per test; a packed FFMA2 holds the issue port 2 cycles, so its floor is 7 + 2 = 9 issue cycles "
-                             "per 32 tests (LDS.128 + 2 FSETP + 1 LOP3 per sphere per 64 rays); see DESIGN.md 5.2-5.3"
+                             "per test for secondary rays and 4 for primary rays; a packed FFMA2 holds the issue port 2 cycles, so the "
+                             "issue floors are 9.0 and 5.5 cycles per 32 tests (LDS.128 + 2-3 ALU ops per sphere per 64 rays); "
+                             "see DESIGN.md 5.2-5.4"
                              if pair_kernel else
                              "15 of the 20 flops' instructions are mandatory separate roundings (parity), so 15 FP32 issue cycles/test "
                              "is the hard floor: frac <= 20/30 = 0.667; see DESIGN.md"),
@@ -370,7 +376,9 @@ def run_gpu_arm(args):
         "config": {"workload": args.workload, "description": desc, "spheres": int(len(spheres)), "width": W, "height": H, "spp": SPP,
                    "max_bounces": 5, "lane_width": LANE_WIDTH, "fma_dot": FMA_DOT,
                    "parallelism": f"sample-sharded x{n_gpus}" + (" + NCCL reduce(sum) to rank 0" if n_gpus > 1 else " (exact running mean)"),
-                   "l2": f"framebuffer working set {H * W * 20 / 1e6:.0f} MB > 126 MB L2; hot loop is FP32-bound, scene in shared memory"},
+                   "l2": (f"accumulator + RGBA8 working set {H * W * 20 / 1e6:.0f} MB" + (" > 126 MB L2" if H * W * 20 > 126e6 else " (fits L2)")
+                          + "; the step is FP32-issue-bound with the sphere tables in shared memory, HBM traffic is < 0.1 % of the "
+                            "step (ncu: dram 7 MB per 42 ms launch), so L2 residency cannot change the number")},
         "rays_per_step": rays_total / args.steps, "gpu_launches": int(launches_total),
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(spheres.nbytes + camera.nbytes),
                 "d2h_bytes_per_step": int(H * W * 4), "steps": e2e_steps, "ms_per_step": e2e_elapsed * 1e3 / e2e_steps,

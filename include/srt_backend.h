@@ -130,6 +130,11 @@ int srt_resolve_sum(srt_backend *b, uint32_t total_samples);
 int srt_read_rgba8(srt_backend *b, void *dst /* W*H*4 bytes */);
 int srt_read_accum(srt_backend *b, float *dst /* W*H*4 floats */);
 int srt_read_primary(srt_backend *b, uint32_t *prim /* 0xFFFFFFFF = miss */, float *t /* 1e30 = miss */);
+/* Upload a HOST accumulator (W*H*4 floats, as srt_read_accum returned it) into PreviousImage:
+ * resume an interrupted accumulation -- the next srt_render continues with
+ * first_sample = the number of samples the buffer holds (checkpoint/resume; the reference keeps
+ * PreviousImage only in its arena, main.cpp:801-804). */
+int srt_write_accum(srt_backend *b, const float *src /* W*H*4 floats */);
 
 /* Device pointers / stream of the current buffers (for collectives and graphs). */
 void *srt_accum_device_ptr(srt_backend *b);

@@ -36,7 +36,7 @@ EXPORTS = [
     "srt_reset_accumulation", "srt_bind_device_buffers", "srt_render", "srt_poll", "srt_wait",
     "srt_resolve_sum", "srt_read_rgba8", "srt_read_accum", "srt_read_primary",
     "srt_accum_device_ptr", "srt_rgba_device_ptr", "srt_cuda_stream", "srt_device_info",
-    "srt_filter_audit",
+    "srt_filter_audit", "srt_write_accum",
 ]
 
 
@@ -83,6 +83,7 @@ def load_library():
     L.srt_read_rgba8.argtypes = [vp, vp]
     L.srt_read_accum.argtypes = [vp, vp]
     L.srt_read_primary.argtypes = [vp, vp, vp]
+    L.srt_write_accum.argtypes = [vp, vp]
     for f in ("srt_accum_device_ptr", "srt_rgba_device_ptr", "srt_cuda_stream"):
         getattr(L, f).argtypes = [vp]
         getattr(L, f).restype = vp
@@ -169,6 +170,12 @@ class Backend:
             out = np.empty((self.height, self.width, 4), np.float32)
         self._check(self.L.srt_read_accum(self.h, out.ctypes.data))
         return out
+
+    def write_accum(self, accum):
+        """Upload a host accumulator (H x W x 4 float32) to resume an accumulation."""
+        a = np.ascontiguousarray(accum, np.float32)
+        assert a.shape == (self.height, self.width, 4)
+        self._check(self.L.srt_write_accum(self.h, a.ctypes.data))
 
     def read_primary(self):
         prim = np.empty((self.height, self.width), np.uint32)

@@ -1111,6 +1111,16 @@ int srt_read_accum(srt_backend *b, float *dst) {
     return SRT_OK;
 }
 
+int srt_write_accum(srt_backend *b, const float *src) {
+    if (!b || !src) return SRT_ERR_INVALID;
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_write_accum: no image (call srt_resize)");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    SRT_CUDA(b, cudaMemcpyAsync(b->d_accum, src, (size_t)b->width * b->height * 16, cudaMemcpyHostToDevice, b->stream));
+    SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+    b->in_flight = false;
+    return SRT_OK;
+}
+
 int srt_read_primary(srt_backend *b, uint32_t *prim, float *t) {
     if (!b) return SRT_ERR_INVALID;
     if (!b->tap_valid) return fail(b, SRT_ERR_INVALID, "srt_read_primary: no render with record_primary since the last reset");

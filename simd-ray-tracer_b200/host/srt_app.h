@@ -80,6 +80,19 @@ bool ReadAccumulator(f32 *Dst);                        // PreviousImage, W*H*4 f
 srt_backend *GetBackend();
 void ComputeCamera(const scene &Scene, f32 Distance, f32 XAngle, f32 YHeight, u32 Width, u32 Height, srt_camera *Out);
 
+// Files either side of the path (srt_files.cpp): accumulator checkpoints and scene descriptions.
+#include <vector>
+struct checkpoint_header { u32 Width, Height, Samples, SceneIndex; u64 StreamBase; u32 LaneWidth, FmaDot; };
+bool SaveCheckpoint(const char *Path, const checkpoint_header &Header, const f32 *Accum);
+bool LoadCheckpoint(const char *Path, checkpoint_header *Header, std::vector<f32> *Accum);
+bool SaveSceneFile(const char *Path, const scene &Scene);
+bool LoadSceneFile(const char *Path, scene *Out);       // allocates Out->ScalarSpheres
+// Replace scene slot `SceneIndex` (0..SceneCount-1) by a loaded scene; the next OnRender with
+// that index uploads it.  Resume: continue an accumulation from a checkpoint (the next
+// OnRender must use the checkpoint's size and scene).
+bool SetScene(u32 SceneIndex, const scene &Scene);
+bool ResumeFromCheckpoint(const checkpoint_header &Header, const f32 *Accum);
+
 // Scene construction (srt_scenes.cpp).
 void BuildScene(u32 SceneIndex, scene *Out);           // allocates Out->ScalarSpheres
 f64 QueryTimestampInMilliseconds();
