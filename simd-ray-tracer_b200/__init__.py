@@ -216,8 +216,53 @@ def load_host_library():
         H = C.CDLL(HOSTLIB_PATH)
         H.srt_host_scene.argtypes = [C.c_uint, C.c_void_p, C.c_uint, C.POINTER(C.c_int), C.c_void_p]
         H.srt_host_camera.argtypes = [C.c_uint, C.c_float, C.c_float, C.c_float, C.c_uint, C.c_uint, C.c_void_p]
+        H.srt_host_save_scene.argtypes = [C.c_uint, C.c_char_p]
+        H.srt_host_load_scene.argtypes = [C.c_uint, C.c_char_p]
+        H.srt_host_reset_scene.argtypes = [C.c_uint]
+        H.srt_host_reset_scene.restype = None
+        H.srt_host_save_checkpoint.argtypes = [C.c_char_p, C.c_void_p, C.c_ulonglong, C.c_void_p]
+        H.srt_host_load_checkpoint.argtypes = [C.c_char_p, C.c_void_p, C.POINTER(C.c_ulonglong), C.c_void_p, C.c_ulonglong]
         _hostlib = H
     return _hostlib
+
+
+def save_scene_file(index, path):
+    """Write scene slot `index` in the text format of host/srt_files.cpp."""
+    if load_host_library().srt_host_save_scene(index, os.fsencode(path)) != 0:
+        raise SrtError(f"cannot write scene file {path}")
+
+
+def load_scene_file(index, path):
+    """Load a scene text file into slot `index` of the host mirror (then host_scene(index))."""
+    if load_host_library().srt_host_load_scene(index, os.fsencode(path)) != 0:
+        raise SrtError(f"cannot load scene file {path}")
+
+
+def reset_scene(index):
+    """Undo load_scene_file: slot `index` is rebuilt as the built-in / synthetic scene on next use."""
+    load_host_library().srt_host_reset_scene(index)
+
+
+def save_checkpoint(path, accum, samples, scene_index, stream_base=0, lane_width=8, fma_dot=1):
+    """Write an accumulator checkpoint (host/srt_files.cpp): accum is H x W x 4 float32."""
+    a = np.ascontiguousarray(accum, np.float32)
+    hdr = np.array([a.shape[1], a.shape[0], samples, scene_index, lane_width, fma_dot], np.uint32)
+    if load_host_library().srt_host_save_checkpoint(os.fsencode(path), hdr.ctypes.data, stream_base, a.ctypes.data) != 0:
+        raise SrtError(f"cannot write checkpoint {path}")
+
+
+def load_checkpoint(path):
+    """-> (accum H x W x 4 float32, dict(width, height, samples, scene_index, lane_width, fma_dot, stream_base))."""
+    H = load_host_library()
+    hdr = np.zeros(6, np.uint32)
+    base = C.c_ulonglong()
+    if H.srt_host_load_checkpoint(os.fsencode(path), hdr.ctypes.data, C.byref(base), None, 0) != 0:
+        raise SrtError(f"{path} is not a checkpoint")
+    a = np.zeros((int(hdr[1]), int(hdr[0]), 4), np.float32)
+    if H.srt_host_load_checkpoint(os.fsencode(path), hdr.ctypes.data, C.byref(base), a.ctypes.data, a.size) != 0:
+        raise SrtError(f"{path} is not a checkpoint")
+    keys = ("width", "height", "samples", "scene_index", "lane_width", "fma_dot")
+    return a, {**{k: int(v) for k, v in zip(keys, hdr)}, "stream_base": int(base.value)}
 
 
 def host_scene(index):

@@ -50,7 +50,7 @@ def build_driver(force=False, verbose=False):
     if force or _newer(DRIVER, srcs_all) or _newer(DRIVER, [LIB]):
         common = ["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-Wall", "-I", os.path.join(ROOT, "include")]
         link = ["-L", PKG, "-lsrt_cuda", "-Wl,-rpath,$ORIGIN", "-lm", "-pthread"]
-        app = [os.path.join(HOST, f) for f in ("srt_app.cpp", "srt_scenes.cpp")]
+        app = [os.path.join(HOST, f) for f in ("srt_app.cpp", "srt_scenes.cpp", "srt_files.cpp")]
         cmds = [
             [*common, *app, os.path.join(HOST, "srt_headless.cpp"), "-o", DRIVER, *link],
             [*common, "-fPIC", "-shared", *app, os.path.join(HOST, "srt_host_capi.cpp"), "-o", HOSTLIB, *link],

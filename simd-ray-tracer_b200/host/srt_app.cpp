@@ -16,6 +16,7 @@
 #include <string.h>
 #include <string>
 #include <time.h>
+#include <vector>
 
 namespace {
 
@@ -35,6 +36,9 @@ u32 g_PreviousRayCount = 0;          // samples already in the accumulator (main
 u32 g_Width = 0, g_Height = 0;       // PreviousImage / CurrentImage size
 bool g_FrameInFlight = false;
 u32 g_InFlightSamples = 0;
+bool g_ResumePending = false;        // ResumeFromCheckpoint armed: the next OnRender uploads g_ResumeAccum
+checkpoint_header g_ResumeHeader;
+std::vector<f32> g_ResumeAccum;
 f32 g_Distance, g_XAngle, g_YHeight; // orbit state (function statics at main.cpp:712-714)
 
 struct vec { f32 x, y, z; };
@@ -127,6 +131,44 @@ void WaitForFrame() {
     if (g_Handle && g_FrameInFlight) srt_wait(g_Handle, nullptr, nullptr);
 }
 
+// Replace a scene slot by a caller-provided scene (copied).  A slot that is currently
+// uploaded is re-uploaded by the next OnRender (which resets the accumulation, as a scene
+// switch does at main.cpp:718-727).
+bool SetScene(u32 SceneIndex, const scene &Scene) {
+    if (SceneIndex >= SceneCount || !Scene.ScalarSpheres || Scene.SphereCount == 0) return false;
+    scalar_sphere *Copy = (scalar_sphere *)malloc(sizeof(scalar_sphere) * Scene.SphereCount);
+    if (!Copy) return false;
+    memcpy(Copy, Scene.ScalarSpheres, sizeof(scalar_sphere) * Scene.SphereCount);
+    if (g_SceneBuilt[SceneIndex]) free(g_Scenes[SceneIndex].ScalarSpheres);
+    g_Scenes[SceneIndex] = Scene;
+    g_Scenes[SceneIndex].ScalarSpheres = Copy;
+    g_SceneBuilt[SceneIndex] = true;
+    if (g_SceneIndex == SceneIndex) g_SceneIndex = 0xFFFFFFFFu;
+    return true;
+}
+
+// Drop a replaced slot: the next GetScene(SceneIndex) rebuilds the built-in / synthetic scene.
+void ResetScene(u32 SceneIndex) {
+    if (SceneIndex >= SceneCount || !g_SceneBuilt[SceneIndex]) return;
+    free(g_Scenes[SceneIndex].ScalarSpheres);
+    g_Scenes[SceneIndex].ScalarSpheres = nullptr;
+    g_SceneBuilt[SceneIndex] = false;
+    if (g_SceneIndex == SceneIndex) g_SceneIndex = 0xFFFFFFFFu;
+}
+
+// Arm a resume: the next OnRender that would start a fresh accumulation (first call, scene
+// switch or resize) with the checkpoint's size and scene uploads the accumulator instead and
+// continues at sample index Header.Samples.  The sample streams are pure functions of
+// (stream_base, sample, pixel), so the continued image is bit-identical to an
+// uninterrupted one.
+bool ResumeFromCheckpoint(const checkpoint_header &Header, const f32 *Accum) {
+    if (!Accum || Header.Width == 0 || Header.Height == 0 || Header.SceneIndex >= SceneCount) return false;
+    g_ResumeHeader = Header;
+    g_ResumeAccum.assign(Accum, Accum + (size_t)Header.Width * Header.Height * 4);
+    g_ResumePending = true;
+    return true;
+}
+
 bool ReadAccumulator(f32 *Dst) { return g_Handle && srt_read_accum(g_Handle, Dst) == SRT_OK; }
 
 bool OnRender(const image &Image, render_params RenderParams, u64 *OutTotalRaysCast, f64 *OutTimeElapsed) {
@@ -198,6 +240,16 @@ bool OnRender(const image &Image, render_params RenderParams, u64 *OutTotalRaysC
             g_Width = Image.Width;
             g_Height = Image.Height;
         } else if (srt_reset_accumulation(g_Handle) != SRT_OK) return Fail("srt_reset_accumulation");
+        if (g_ResumePending) {
+            g_ResumePending = false;
+            if (g_ResumeHeader.Width != g_Width || g_ResumeHeader.Height != g_Height || g_ResumeHeader.SceneIndex != g_SceneIndex ||
+                g_ResumeHeader.StreamBase != g_Backend.StreamBase)
+                return Fail("OnRender: checkpoint does not match the image size, scene or stream base");
+            if (srt_write_accum(g_Handle, g_ResumeAccum.data()) != SRT_OK) return Fail("srt_write_accum");
+            g_PreviousRayCount = g_ResumeHeader.Samples;
+            g_ResumeAccum.clear();
+            g_ResumeAccum.shrink_to_fit();
+        }
     } else if (Complete) {
         if (CopyToOutput && !Publish()) return false;
         g_PreviousRayCount += g_InFlightSamples;                                // PreviousRayCount += 1, main.cpp:806

@@ -91,6 +91,7 @@ bool LoadSceneFile(const char *Path, scene *Out);       // allocates Out->Scalar
 // that index uploads it.  Resume: continue an accumulation from a checkpoint (the next
 // OnRender must use the checkpoint's size and scene).
 bool SetScene(u32 SceneIndex, const scene &Scene);
+void ResetScene(u32 SceneIndex);                        // back to the built-in scene of that slot
 bool ResumeFromCheckpoint(const checkpoint_header &Header, const f32 *Accum);
 
 // Scene construction (srt_scenes.cpp).

@@ -32,7 +32,11 @@ static void Usage() {
             "usage: srt_headless [--scene 0..4] [--width W] [--height H] [--spp N] [--spf K]\n"
             "                    [--simd 0|1] [--lanes 4|8] [--fma 0|1] [--device D] [--stream-base B]\n"
             "                    [--orbit FRAMES] [--out image.ppm] [--accum accum.f32]\n"
+            "                    [--scene-file in.scene] [--dump-scene out.scene]\n"
+            "                    [--checkpoint out.ckpt] [--resume in.ckpt]\n"
             "  scenes: 0 RGB Glass, 1 Floating Spheres, 2 One Weekend, 3 synthetic 1,024, 4 synthetic 65,536\n"
+            "  --scene-file replaces slot --scene by the file's scene; --dump-scene writes slot --scene as text.\n"
+            "  --resume continues a checkpoint (same size, scene, stream base): --spp more samples are added.\n"
             "  --spf: samples per OnRender frame (reference: 1).  --orbit: hold key A for FRAMES frames first.\n");
 }
 
@@ -40,7 +44,7 @@ int main(int argc, char **argv) {
     u32 Scene = 0, W = 1280, H = 720, Spp = 1, Spf = 1, Orbit = 0;
     bool Simd = true;
     backend_params BP;
-    const char *Out = nullptr, *AccumOut = nullptr;
+    const char *Out = nullptr, *AccumOut = nullptr, *SceneFile = nullptr, *DumpScene = nullptr, *CkptOut = nullptr, *CkptIn = nullptr;
     for (int i = 1; i < argc; ++i) {
         std::string A = argv[i];
         auto Next = [&]() -> const char * { if (i + 1 >= argc) { Usage(); exit(2); } return argv[++i]; };
@@ -57,12 +61,41 @@ int main(int argc, char **argv) {
         else if (A == "--orbit") Orbit = atoi(Next());
         else if (A == "--out") Out = Next();
         else if (A == "--accum") AccumOut = Next();
+        else if (A == "--scene-file") SceneFile = Next();
+        else if (A == "--dump-scene") DumpScene = Next();
+        else if (A == "--checkpoint") CkptOut = Next();
+        else if (A == "--resume") CkptIn = Next();
         else { Usage(); return 2; }
     }
     if (Spf == 0) Spf = 1;
     if (Spp == 0) Spp = 1;
     BP.SamplesPerFrame = Spf;
     SetBackendParams(BP);
+
+    if (Scene >= SceneCount) { Usage(); return 2; }
+    if (SceneFile) {
+        scene Loaded;
+        if (!LoadSceneFile(SceneFile, &Loaded) || !SetScene(Scene, Loaded)) { fprintf(stderr, "cannot load scene file %s\n", SceneFile); return 1; }
+        free(Loaded.ScalarSpheres);
+    }
+    if (DumpScene) {
+        if (!SaveSceneFile(DumpScene, *GetScene(Scene))) { fprintf(stderr, "cannot write %s\n", DumpScene); return 1; }
+        if (!Out && !AccumOut && !CkptOut) return 0;       // dump only: no GPU needed
+    }
+    u32 ResumedSamples = 0;
+    if (CkptIn) {
+        checkpoint_header Hd;
+        std::vector<f32> Acc;
+        if (!LoadCheckpoint(CkptIn, &Hd, &Acc)) { fprintf(stderr, "cannot read checkpoint %s\n", CkptIn); return 1; }
+        if (Hd.SceneIndex != Scene || Hd.LaneWidth != (Simd ? BP.LaneWidth : 1u) || Hd.FmaDot != (u32)(Simd && BP.FmaDot)) {
+            fprintf(stderr, "checkpoint %s was written for scene %u, lanes %u, fma %u\n", CkptIn, Hd.SceneIndex, Hd.LaneWidth, Hd.FmaDot);
+            return 1;
+        }
+        W = Hd.Width; H = Hd.Height; BP.StreamBase = Hd.StreamBase;
+        SetBackendParams(BP);
+        if (!ResumeFromCheckpoint(Hd, Acc.data())) { fprintf(stderr, "bad checkpoint %s\n", CkptIn); return 1; }
+        ResumedSamples = Hd.Samples;
+    }
 
     init_params Init = {};
     if (!OnInit(&Init)) { fprintf(stderr, "OnInit failed: %s\n", LastError()); return 1; }
@@ -104,6 +137,12 @@ int main(int argc, char **argv) {
     const f64 Wall = QueryTimestampInMilliseconds() - Wall0;
 
     if (Out && !WritePpm(Out, Present.data(), W, H)) { fprintf(stderr, "cannot write %s\n", Out); return 1; }
+    if (CkptOut) {
+        std::vector<f32> Acc((size_t)W * H * 4);
+        ReadAccumulator(Acc.data());
+        checkpoint_header Hd = { W, H, GetAccumulatedSampleCount(), Scene, BP.StreamBase, Simd ? BP.LaneWidth : 1u, (u32)(Simd && BP.FmaDot) };
+        if (!SaveCheckpoint(CkptOut, Hd, Acc.data())) { fprintf(stderr, "cannot write %s\n", CkptOut); return 1; }
+    }
     if (AccumOut) {
         std::vector<f32> Acc((size_t)W * H * 4);
         ReadAccumulator(Acc.data());
@@ -117,9 +156,9 @@ int main(int argc, char **argv) {
     const scene *S = GetScene(Scene);
     printf("{\"scene\": \"%s\", \"spheres\": %u, \"width\": %u, \"height\": %u, \"spp\": %u, \"frames\": %zu, "
            "\"rays\": %llu, \"device_ms\": %.4f, \"wall_ms\": %.3f, \"mrays_per_s\": %.2f, "
-           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u}\n",
+           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u, \"resumed_from\": %u}\n",
            S->Name, S->SphereCount, W, H, Frames * Spf, FrameMs.size(), (unsigned long long)TotalRays, TotalMs, Wall,
-           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount());
+           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount(), ResumedSamples);
     OnShutdown();
     return 0;
 }

@@ -1,6 +1,7 @@
 // srt_host_capi.cpp -- C entry points over the host mirror's scene/camera logic, so the
 // tests can compare it with goldens without a GPU (no backend call in here).
 #include "srt_app.h"
+#include <stdlib.h>
 #include <string.h>
 
 extern "C" {
@@ -22,6 +23,43 @@ int srt_host_scene(unsigned index, void *out, unsigned capacity, int *use_sky, f
 void srt_host_camera(unsigned index, float distance, float x_angle, float y_height, unsigned w, unsigned h, srt_camera *out) {
     const scene *S = GetScene(index);
     if (S) ComputeCamera(*S, distance, x_angle, y_height, w, h, out);
+}
+
+
+// Scene text format round trip (srt_files.cpp): write slot `index` / load a file into slot `index`.
+int srt_host_save_scene(unsigned index, const char *path) {
+    const scene *S = GetScene(index);
+    return S && SaveSceneFile(path, *S) ? 0 : -1;
+}
+
+int srt_host_load_scene(unsigned index, const char *path) {
+    scene Loaded;
+    if (!LoadSceneFile(path, &Loaded)) return -1;
+    const bool Ok = SetScene(index, Loaded);
+    free(Loaded.ScalarSpheres);
+    return Ok ? 0 : -1;
+}
+
+void srt_host_reset_scene(unsigned index) { ResetScene(index); }
+
+// Checkpoint container round trip.  header = {width, height, samples, scene_index, lane_width, fma_dot}.
+int srt_host_save_checkpoint(const char *path, const unsigned *header, unsigned long long stream_base, const float *accum) {
+    checkpoint_header H = { header[0], header[1], header[2], header[3], stream_base, header[4], header[5] };
+    return SaveCheckpoint(path, H, accum) ? 0 : -1;
+}
+
+// accum == NULL: header only.  Returns -1 on a malformed file, -2 when capacity (floats) is too small.
+int srt_host_load_checkpoint(const char *path, unsigned *header, unsigned long long *stream_base, float *accum, unsigned long long capacity) {
+    checkpoint_header H;
+    std::vector<f32> A;
+    if (!LoadCheckpoint(path, &H, &A)) return -1;
+    header[0] = H.Width; header[1] = H.Height; header[2] = H.Samples; header[3] = H.SceneIndex; header[4] = H.LaneWidth; header[5] = H.FmaDot;
+    if (stream_base) *stream_base = H.StreamBase;
+    if (accum) {
+        if (capacity < A.size()) return -2;
+        memcpy(accum, A.data(), A.size() * sizeof(f32));
+    }
+    return 0;
 }
 
 }

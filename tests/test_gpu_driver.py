@@ -46,3 +46,49 @@ def test_driver_samples_per_frame_and_orbit(srt, oracle, tmp_path):
     s3, a3, _ = run_driver(srt, tmp_path, "--scene", 0, "--width", w, "--height", h, "--spp", 2, "--orbit", 3)
     assert s3["samples_accumulated"] == 2 and np.isfinite(a3).all()
     assert not np.array_equal(a3[: a1.size], a1)            # camera moved -> different image
+
+
+def test_write_accum_resume_is_bit_exact(srt, oracle):
+    """N2: 4 spp, read the accumulator, upload it into a NEW backend, 4 more spp == 8 spp straight."""
+    w, h = 160, 90
+    sp, sky, hdr = srt.host_scene(2)
+    cam = srt.host_camera(2, w, h)
+    for lanes, fma in ((8, 1), (1, 0)):
+        full = srt.Backend()
+        full.set_scene(sp, sky, lanes, fma); full.resize(w, h)
+        full.render(cam, 0, 8); _, rays_full = full.wait()
+        a = srt.Backend()
+        a.set_scene(sp, sky, lanes, fma); a.resize(w, h)
+        a.render(cam, 0, 4); _, r1 = a.wait()
+        half = a.read_accum()
+        b = srt.Backend()
+        b.set_scene(sp, sky, lanes, fma); b.resize(w, h)
+        b.write_accum(half)
+        b.render(cam, 4, 4); _, r2 = b.wait()
+        assert np.array_equal(b.read_accum().view(np.uint32), full.read_accum().view(np.uint32))
+        assert np.array_equal(b.read_rgba8(), full.read_rgba8()) and r1 + r2 == rays_full
+        for x in (full, a, b):
+            x.close()
+
+
+def test_driver_checkpoint_resume_and_scene_file(srt, oracle, tmp_path):
+    w, h = 96, 54
+    ck = tmp_path / "half.ckpt"
+    sf = tmp_path / "two.scene"
+    s_full, a_full, ppm_full = run_driver(srt, tmp_path, "--scene", 1, "--width", w, "--height", h, "--spp", 6)
+    s1, _, _ = run_driver(srt, tmp_path, "--scene", 1, "--width", w, "--height", h, "--spp", 2, "--checkpoint", ck)
+    acc, hd = srt.load_checkpoint(ck)
+    assert hd["samples"] == 2 and hd["width"] == w and hd["height"] == h and hd["scene_index"] == 1
+    s2, a2, ppm2 = run_driver(srt, tmp_path, "--scene", 1, "--spp", 4, "--resume", ck)
+    assert s2["resumed_from"] == 2 and s2["samples_accumulated"] == 6
+    assert np.array_equal(a2.view(np.uint32), a_full.view(np.uint32)) and ppm2 == ppm_full
+    assert s1["rays"] + s2["rays"] == s_full["rays"]
+    # a checkpoint for another scene is refused
+    res = subprocess.run([srt.DRIVER_PATH, "--scene", "0", "--spp", "1", "--resume", str(ck)], capture_output=True, text=True, timeout=120)
+    assert res.returncode != 0 and "checkpoint" in res.stderr
+    # scene file: dump scene 2, load it into slot 0, render == scene 2 rendered directly (same default camera)
+    res = subprocess.run([srt.DRIVER_PATH, "--scene", "2", "--dump-scene", str(sf)], capture_output=True, text=True, timeout=120)
+    assert res.returncode == 0, res.stderr
+    s_a, a_a, _ = run_driver(srt, tmp_path, "--scene", 2, "--width", w, "--height", h, "--spp", 2)
+    s_b, a_b, _ = run_driver(srt, tmp_path, "--scene", 0, "--scene-file", sf, "--width", w, "--height", h, "--spp", 2)
+    assert np.array_equal(a_a.view(np.uint32), a_b.view(np.uint32)) and s_a["rays"] == s_b["rays"] and s_b["spheres"] == s_a["spheres"]

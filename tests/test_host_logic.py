@@ -49,3 +49,59 @@ def test_synthetic_scenes(srt, scene, count):
     assert (sp["ior"] == 0).all()
     frac_em = (sp["emissive"][1:, :3].sum(1) > 0).mean()
     assert 0.08 < frac_em < 0.17
+
+
+# ---- files either side of the path (host/srt_files.cpp): scene text format, checkpoints -----
+@pytest.mark.parametrize("scene", [0, 1, 2, 3])
+def test_scene_file_round_trip_is_bit_exact(srt, tmp_path, scene):
+    sp, sky, hdr = srt.host_scene(scene)
+    path = tmp_path / "s.scene"
+    srt.save_scene_file(scene, path)
+    srt.load_scene_file(4, path)                               # into the 64K slot (replaced)
+    sp2, sky2, hdr2 = srt.host_scene(4)
+    srt.reset_scene(4)
+    assert len(sp2) == len(sp) and sky2 == sky and hdr2.tobytes() == hdr.tobytes()
+    for f in ("position", "radius", "color", "emissive", "specular", "ior"):
+        a, b = np.ascontiguousarray(sp[f]), np.ascontiguousarray(sp2[f])
+        if a.ndim == 2:
+            a, b = np.ascontiguousarray(a[:, :3]), np.ascontiguousarray(b[:, :3])
+        assert a.tobytes() == b.tobytes(), f
+
+
+def test_scene_file_hand_written_and_malformed(srt, tmp_path):
+    good = tmp_path / "g.scene"
+    good.write_text("# two spheres\nsky 1\nlookat 0 0.5 0\ncamera 3 0.25 1\n"
+                    "sphere 0 -100 0 100  0.5 0.5 0.5  0 0 0  0 0\n"
+                    "  sphere 0 0.5 0 0.5  1 1 1  0 0 0  1 1.5\n\n")
+    srt.load_scene_file(3, good)
+    sp, sky, hdr = srt.host_scene(3)
+    assert len(sp) == 2 and sky and hdr.tolist() == [0.0, 0.5, 0.0, 3.0, 0.25, 1.0]
+    assert sp["radius"].tolist() == [100.0, 0.5] and sp["ior"].tolist() == [0.0, 1.5] and sp["specular"].tolist() == [0.0, 1.0]
+    for text in ("sphere 1 2 3\n", "sky 1\n", "bogus 1\nsphere 0 0 0 1 1 1 1 0 0 0 0 0\n"):
+        bad = tmp_path / "b.scene"
+        bad.write_text(text)
+        with pytest.raises(srt.SrtError):
+            srt.load_scene_file(3, bad)
+    with pytest.raises(srt.SrtError):
+        srt.load_scene_file(3, tmp_path / "missing.scene")
+    assert len(srt.host_scene(3)[0]) == 2                      # failed loads leave the slot alone
+    srt.reset_scene(3)
+    assert len(srt.host_scene(3)[0]) == 1024
+
+
+def test_checkpoint_round_trip_and_rejects_damage(srt, tmp_path):
+    rng = np.random.default_rng(5)
+    acc = rng.random((7, 13, 4), dtype=np.float32)
+    acc[0, 0, 0] = np.float32(np.inf)
+    path = tmp_path / "a.ckpt"
+    srt.save_checkpoint(path, acc, samples=11, scene_index=2, stream_base=(1 << 40) + 3, lane_width=4, fma_dot=0)
+    a2, h = srt.load_checkpoint(path)
+    assert a2.tobytes() == acc.tobytes()
+    assert h == {"width": 13, "height": 7, "samples": 11, "scene_index": 2, "lane_width": 4, "fma_dot": 0, "stream_base": (1 << 40) + 3}
+    raw = path.read_bytes()
+    assert raw[:8] == b"SRTCKPT1" and len(raw) == 8 + 32 + acc.nbytes
+    for damaged in (raw[:-4], raw + b"\0", b"XRTCKPT1" + raw[8:], raw[:20]):
+        bad = tmp_path / "bad.ckpt"
+        bad.write_bytes(damaged)
+        with pytest.raises(srt.SrtError):
+            srt.load_checkpoint(bad)
