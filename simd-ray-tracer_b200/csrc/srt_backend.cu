@@ -140,8 +140,8 @@ render_paths(const __grid_constant__ KernelParams P) {
 // the regenerate / shade phases are plain run-time loops over the two slots.
 // ------------------------------------------------------------------------------------------
 enum : int { S_OX, S_OY, S_OZ, S_DX, S_DY, S_DZ, S_AX, S_AY, S_AZ, S_LX, S_LY, S_LZ, S_MX, S_MY, S_MZ,
-             S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_COUNT };
-constexpr uint32_t kFlagBounceMask = 7u, kFlagActive = 8u, kFlagDone = 16u;
+             S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_KEND, S_COUNT };
+constexpr uint32_t kFlagBounceMask = 7u, kFlagActive = 8u, kFlagDone = 16u, kFlagPending = 32u;
 
 template <int W, bool FMA, int THREADS, int MINB>
 __global__ void __launch_bounds__(THREADS, MINB)
@@ -380,6 +380,7 @@ render_pool(const __grid_constant__ KernelParams P) {
         for (uint32_t i = tid; i < NS; i += THREADS) {
             SRT_SU(S_PIX, i) = kInvalidPixel;
             SRT_SU(S_K, i) = k_end;
+            SRT_SU(S_KEND, i) = k_end;
             SRT_SU(S_FLAGS, i) = 0u;
         }
         for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? i : kRingEmpty; ring1[i] = kRingEmpty; }
@@ -391,10 +392,11 @@ render_pool(const __grid_constant__ KernelParams P) {
     }
     __syncthreads();
     unsigned long long rays = 0;
+    bool hungry = false;
 
     for (;;) {
         uint32_t kind = 0, n = 0, pos = 0;
-        if (lane == 0) pool_acquire(ctl, NS, kind, n, pos);
+        if (lane == 0) pool_acquire(ctl, NS, hungry, kind, n, pos);
         kind = __shfl_sync(0xFFFFFFFFu, kind, 0);
         n = __shfl_sync(0xFFFFFFFFu, n, 0);
         pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
@@ -410,20 +412,32 @@ render_pool(const __grid_constant__ KernelParams P) {
         pk2 ox, oy, oz, dx, dy, dz;
         CandQueue queue;                 // resident tables: one queue for either kind of pass
         uint32_t qn = 0;
+        uint32_t pend = 0;               // bit r: slot of half r waits for the preceding sample chunk of its pixel
+        bool any_real = true;
         if (kind == 0) {
-            // ---- 64 slots that need a new primary ray: finish pixels, fetch new ones (A1) ----
+            // ---- 64 slots that need a new primary ray: finish items, fetch new ones (A1) -------
+            bool real = false;
 #pragma unroll 1
             for (int r = 0; r < 2; ++r) {
                 const uint32_t s = r ? id1 : id0;
                 const bool valid = s != kRingEmpty;
-                uint32_t pix = kInvalidPixel, k = k_end, pxy = 0;
-                if (valid) { pix = SRT_SU(S_PIX, s); k = SRT_SU(S_K, s); pxy = SRT_SU(S_PXY, s); }
-                bool need = valid && (k == k_end);
+                uint32_t pix = kInvalidPixel, k = k_end, kend = k_end, pxy = 0;
+                bool pending = false;
+                if (valid) {
+                    pix = SRT_SU(S_PIX, s); k = SRT_SU(S_K, s); kend = SRT_SU(S_KEND, s); pxy = SRT_SU(S_PXY, s);
+                    pending = (SRT_SU(S_FLAGS, s) & kFlagPending) != 0u;
+                }
+                bool need = valid && !pending && (k == kend);
                 if (need && pix != kInvalidPixel) {
-                    // A8 result + A9 tonemap/pack, main.cpp:484-492
+                    // the item's samples are folded: A8 result (+ A9 tonemap/pack after the pixel's last chunk), main.cpp:484-492
                     const float mx = SRT_ST(S_MX, s), my = SRT_ST(S_MY, s), mz = SRT_ST(S_MZ, s);
                     P.accum[pix] = make_float4(mx, my, mz, 1.0f);
-                    if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mx, my, mz);
+                    if (kend == k_end) {
+                        if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mx, my, mz);
+                    } else {
+                        __threadfence();                                   // accum before the chunk count
+                        *(volatile uint32_t *)&P.done[pix] = P.done_tag | ((kend - P.first_sample) / P.chunk_span);
+                    }
                     pix = kInvalidPixel;
                 }
                 bool retire = false;
@@ -437,36 +451,56 @@ render_pool(const __grid_constant__ KernelParams P) {
                         const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
                         uint32_t px, py;
                         if (item >= P.total_items) { retire = true; need = false; }
-                        else if (item_to_pixel(P, item, px, py)) {
-                            pix = py * P.width + px;
-                            pxy = px | (py << 16);
-                            k = P.first_sample;
-                            need = false;
-                            float4 prev = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1), zeroed arena
-                            if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) prev = P.accum[pix];
-                            SRT_ST(S_MX, s) = prev.x; SRT_ST(S_MY, s) = prev.y; SRT_ST(S_MZ, s) = prev.z;
+                        else {
+                            const uint32_t c = item / P.items_per_gen;      // chunk-major: every pixel's chunk c before any chunk c+1
+                            if (item_to_pixel(P, item - c * P.items_per_gen, px, py)) {
+                                pix = py * P.width + px;
+                                pxy = px | (py << 16);
+                                k = P.first_sample + c * P.chunk_span;
+                                kend = (k_end - k <= P.chunk_span) ? k_end : k + P.chunk_span;
+                                need = false;
+                                pending = true;
+                            }
                         }
                     }
                     m = __ballot_sync(0xFFFFFFFFu, need);
+                }
+                if (pending) {
+                    // the running mean is sequential in k (main.cpp:484-489): chunk c starts from the mean chunk c-1 published
+                    const uint32_t c = (k - P.first_sample) / P.chunk_span;
+                    if (c == 0u || *(volatile uint32_t *)&P.done[pix] == (P.done_tag | c)) {
+                        float4 prev = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1), zeroed arena
+                        if (c != 0u) { __threadfence(); prev = __ldcg(&P.accum[pix]); }
+                        else if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) prev = __ldcg(&P.accum[pix]);
+                        SRT_ST(S_MX, s) = prev.x; SRT_ST(S_MY, s) = prev.y; SRT_ST(S_MZ, s) = prev.z;
+                        pending = false;
+                    }
                 }
                 const unsigned rm = __ballot_sync(0xFFFFFFFFu, retire);
                 if (rm && lane == (unsigned)(__ffs(rm) - 1)) atomicAdd(&ctl->retired, (unsigned)__popc(rm));
                 f3 o = cam_o, d = mk3(0.0f, 0.0f, 0.0f);
                 if (retire) { SRT_SU(S_PIX, s) = kInvalidPixel; if (r) id1 = kRingEmpty; else id0 = kRingEmpty; }
-                else if (valid) {
+                else if (valid && pending) {
+                    SRT_SU(S_PIX, s) = pix; SRT_SU(S_K, s) = k; SRT_SU(S_KEND, s) = kend; SRT_SU(S_PXY, s) = pxy; SRT_SU(S_FLAGS, s) = kFlagPending;
+                    pend |= 1u << r;
+                } else if (valid) {
                     uint64_t rng;
                     primary_ray<true>(P, pxy & 0xFFFFu, pxy >> 16, pix, k, rng, o, d);
                     SRT_ST(S_AX, s) = 1.0f; SRT_ST(S_AY, s) = 1.0f; SRT_ST(S_AZ, s) = 1.0f;
                     SRT_ST(S_LX, s) = 0.0f; SRT_ST(S_LY, s) = 0.0f; SRT_ST(S_LZ, s) = 0.0f;
                     SRT_SU(S_RNG_LO, s) = (uint32_t)rng; SRT_SU(S_RNG_HI, s) = (uint32_t)(rng >> 32);
-                    SRT_SU(S_PIX, s) = pix; SRT_SU(S_K, s) = k; SRT_SU(S_PXY, s) = pxy; SRT_SU(S_FLAGS, s) = 0u;   // bounce 0
+                    SRT_SU(S_PIX, s) = pix; SRT_SU(S_K, s) = k; SRT_SU(S_KEND, s) = kend; SRT_SU(S_PXY, s) = pxy; SRT_SU(S_FLAGS, s) = 0u;   // bounce 0
+                    real = true;
                 }
                 if (r) { o1 = o; d1 = d; } else { o0 = o; d0 = d; }
             }
+            any_real = __any_sync(0xFFFFFFFFu, real);
             ox = pk_make(cam_o.x, cam_o.x); oy = pk_make(cam_o.y, cam_o.y); oz = pk_make(cam_o.z, cam_o.z);
             dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
             const ScanPrimary rays_p = make_scan_primary(cam_o.x, cam_o.y, cam_o.z, dx, dy, dz);
-            if (STREAM) {
+            if (!any_real) {
+                // nothing runnable in this batch (slots waiting for a chunk, or retiring)
+            } else if (STREAM) {
                 stream_pass<SUBP, W, FMA>(ws, P.ptab, P.spheres, P.n_pad, P.n_spheres, rays_p, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
             } else {
                 scan_primary_tile<SUBP>(s_ptab, P.n_pad, 0u, rays_p, queue, qn);
@@ -492,17 +526,21 @@ render_pool(const __grid_constant__ KernelParams P) {
                 scan_general_tile<SUB>(s_scan, P.n_pad, 0u, rays_s, queue, qn);
             }
         }
-        if (!STREAM) {
-            const FetchResident fetch = {s_scan, s_r2};
-            select_update<W, FMA>(fetch, P.n_spheres, queue, qn, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+        if (any_real) {
+            if (!STREAM) {
+                const FetchResident fetch = {s_scan, s_r2};
+                select_update<W, FMA>(fetch, P.n_spheres, queue, qn, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+            }
+            select_finish<W, FMA>(P.spheres, P.n_pad, b0, b1, ox, oy, oz, dx, dy, dz, h0, h1);
         }
-        select_finish<W, FMA>(P.spheres, P.n_pad, b0, b1, ox, oy, oz, dx, dy, dz, h0, h1);
+        hungry = !any_real && __any_sync(0xFFFFFFFFu, pend != 0u);
 
         // ---- shade / scatter, one half after the other; push every slot to its next ring ------
 #pragma unroll 1
         for (int r = 0; r < 2; ++r) {
             const uint32_t s = r ? id1 : id0;
-            const bool valid = s != kRingEmpty;
+            const bool waits = ((pend >> r) & 1u) != 0u;
+            const bool valid = s != kRingEmpty && !waits;
             bool ended = false;
             if (valid) {
                 const Hit h = r ? h1 : h0;
@@ -534,7 +572,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                     SRT_SU(S_FLAGS, s) = bounce;
                 }
             }
-            pool_push(ctl, ring0, RCAP - 1u, 0, valid && ended, s, lane);
+            pool_push(ctl, ring0, RCAP - 1u, 0, (valid && ended) || waits, s, lane);
             pool_push(ctl, ring1, RCAP - 1u, 1, valid && !ended, s, lane);
         }
         if (lane == 0) atomicSub(&ctl->inflight, 1u);
@@ -657,6 +695,8 @@ struct srt_backend {
     bool tap_valid = false;
     // counters: [0..7] rays (u64), [8..11] work counter
     unsigned char *d_counters = nullptr;
+    uint32_t *d_done = nullptr;          // pool kernel: per-pixel chunk counters (KernelParams::done)
+    uint32_t pool_chunk = 0;             // samples per work item, 0 = kPoolChunkSamples (SRT_POOL_CHUNK)
     unsigned long long *h_rays = nullptr;   // pinned
     bool in_flight = false;
     uint64_t launches = 0;
@@ -711,6 +751,7 @@ static PairConfig pick_pairs_kernel(const srt_scene_options &o) {
 // Pool kernel (srt_pool.cuh): CTA-owned path slots, primary / secondary warp passes.
 constexpr int kPoolThreads = 256;
 constexpr int kPoolMinBlocks = 2;
+constexpr uint32_t kPoolChunkSamples = 1;   // samples per pool work item (measured best: 1; SRT_POOL_CHUNK overrides)
 // Unroll of the secondary-ray scan: 32 spheres per loop body is 3 % faster on >= 768 spheres, 16
 // is 4-9 % faster below (the bodies share the 6 KB L0 / 32 KB L1.5 instruction caches with the
 // primary scan, select and shade code).  Measured on B200, profiles/r1d_pool_tuning.log.
@@ -777,6 +818,7 @@ void srt_destroy(srt_backend *b) {
     cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
     cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
     cudaFree(b->d_counters);
+    cudaFree(b->d_done);
     if (b->h_rays) cudaFreeHost(b->h_rays);
     if (b->ev_start) cudaEventDestroy(b->ev_start);
     if (b->ev_stop) cudaEventDestroy(b->ev_stop);
@@ -853,6 +895,8 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
     b->opt = *options;
     b->variant = options->_reserved;
     if (const char *v = getenv("SRT_KERNEL_VARIANT")) b->variant = atoi(v);
+    b->pool_chunk = 0;
+    if (const char *v = getenv("SRT_POOL_CHUNK")) b->pool_chunk = (uint32_t)std::max(0, atoi(v));
     // Path start-up costs the whole warp ~200 issue slots however few lanes need it.  For
     // tiny scenes (intersection pass cheaper than that) a warp therefore refills only once
     // all its lanes are idle, which also keeps its primary rays coherent; measured on B200:
@@ -884,7 +928,8 @@ int srt_resize(srt_backend *b, uint32_t width, uint32_t height) {
     if (rc) return rc;
     const size_t n = (size_t)width * height;
     if (width != b->width || height != b->height || !b->d_accum_own) {
-        cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own); cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
+        cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own); cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t); cudaFree(b->d_done);
+        b->d_done = nullptr;
         b->d_accum_own = nullptr; b->d_rgba_own = nullptr; b->d_tap_prim = nullptr; b->d_tap_t = nullptr;
         SRT_CUDA(b, cudaMalloc(&b->d_accum_own, n * sizeof(float4)));
         SRT_CUDA(b, cudaMalloc(&b->d_rgba_own, n * sizeof(uint32_t)));
@@ -950,6 +995,8 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.rays = (unsigned long long *)b->d_counters;
     P.work_counter = (unsigned int *)(b->d_counters + 8);
     P.debug = (unsigned long long *)(b->d_counters + 16);
+    P.items_per_gen = P.total_items;
+    P.chunk_span = 0;
     return SRT_OK;
 }
 
@@ -987,6 +1034,24 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         b->tap_valid = true;
     }
 
+    if (pool) {
+        // work items = (sample chunk, pixel), chunk-major.  A pixel's chunks are folded in order through
+        // done[pix]; short chunks keep the end of the launch short (few slots left with many samples to go).
+        if (!b->d_done) {   // 0xFF..: no launch tag matches (recycled device memory may hold another backend's counts)
+            SRT_CUDA(b, cudaMalloc(&b->d_done, (size_t)b->width * b->height * sizeof(uint32_t)));
+            SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
+        }
+        uint32_t chunk = b->pool_chunk ? b->pool_chunk : kPoolChunkSamples;
+        const uint32_t max_chunks = std::min<uint32_t>(4095u, 0xF0000000u / P.items_per_gen);
+        if ((args->n_samples + chunk - 1) / chunk > max_chunks) chunk = (args->n_samples + max_chunks - 1) / max_chunks;
+        const uint32_t n_chunks = (args->n_samples + chunk - 1) / chunk;
+        P.chunk_span = chunk * args->sample_stride;
+        P.total_items = P.items_per_gen * n_chunks;
+        P.done = b->d_done;
+        P.done_tag = (uint32_t)((b->launches + 1) & 0xFFFFFu) << 12;
+        if (P.done_tag == 0u && n_chunks > 1u)   // sequence wrapped: forget counts of 2^20 launches ago
+            SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
+    }
     render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, b->n_pad, stream) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
     const int threads = pool ? kPoolThreads : pairs ? pc.threads : kBlockThreads;
     const size_t smem = pool ? pool_smem_bytes(b->n_pad, kPoolThreads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);

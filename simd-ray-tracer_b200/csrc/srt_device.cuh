@@ -137,6 +137,12 @@ struct KernelParams {
     unsigned long long *rays;
     unsigned int *work_counter;
     unsigned long long *debug;   // optional diagnostics (pool kernel)
+    // pool kernel work items: (sample chunk, pixel), chunk-major, so that the end of a launch does not
+    // wait for single pixels to run all their samples
+    uint32_t *done;              // per pixel: done_tag | number of chunks folded into accum[pix] in this launch
+    uint32_t done_tag;           // launch sequence number << 12
+    uint32_t chunk_span;         // samples per chunk * sample_stride
+    uint32_t items_per_gen;      // blocks_x * blocks_y * 32; pool: total_items = items_per_gen * chunks
     uint32_t regen_threshold;    // start new paths once this many lanes of a warp are idle
     float neg_one, one;          // -1.0f / +1.0f, deliberately opaque to the compiler (srt_packed.cuh)
 };

@@ -52,9 +52,15 @@ __device__ __forceinline__ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want
     return false;
 }
 
-// Lane 0 decides; returns n == 0 when every slot of the CTA has retired.
-__device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, uint32_t &kind, uint32_t &n, uint32_t &pos) {
+// Lane 0 decides; returns n == 0 when every slot of the CTA has retired.  `hungry`: the caller's
+// last batch held no runnable path (all its slots wait for another slot's sample chunk): it may
+// take a partial batch of secondary rays, so the paths being waited for always advance.
+__device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, bool hungry, uint32_t &kind, uint32_t &n, uint32_t &pos) {
     n = 0; kind = 0; pos = 0;
+    if (hungry) {
+        __nanosleep(200);
+        if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
+    }
     for (;;) {
         if (pool_try_take(ctl, 0, 64u, n, pos)) { kind = 0; return; }
         if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }

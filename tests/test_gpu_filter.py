@@ -226,3 +226,43 @@ def test_nested_and_tied_spheres(backend, srt, oracle, mode):
     backend.set_scene(sp, True, W, bool(fma))
     a = backend.filter_audit(cam, 0, 2)
     assert a["violations"] == 0, a
+
+
+@pytest.mark.parametrize("chunk", ["", "1", "3", "1000"])
+def test_pool_sample_chunks_fold_in_order(srt, oracle, monkeypatch, chunk):
+    """Pool work items are (sample chunk, pixel); a pixel's chunks must fold into the running mean
+    in sample order even when far more path slots than pixels exist (every slot of the grid then
+    holds a later chunk of some pixel and waits for the preceding one)."""
+    if chunk:
+        monkeypatch.setenv("SRT_POOL_CHUNK", chunk)
+    else:
+        monkeypatch.delenv("SRT_POOL_CHUNK", raising=False)
+    spheres, sky, hdr = srt.host_scene(2)
+    b = srt.Backend(0)
+    try:
+        for (w, h, spp, first) in ((1, 1, 40, 0), (5, 3, 24, 0), (33, 17, 9, 2), (160, 90, 7, 0)):
+            cam = srt.host_camera(2, w, h, hdr)
+            o = oracle.render(spheres, sky, 8, 1, cam, w, h, 0, first + spp)
+            b.set_scene(spheres, sky, 8, True)
+            b.resize(w, h)
+            rays = 0
+            if first:
+                b.render(cam, 0, first)
+                rays += b.wait()[1]
+            b.render(cam, first, spp)
+            rays += b.wait()[1]
+            assert np.array_equal(b.read_accum().view(np.uint32), o["accum"].view(np.uint32)), (w, h)
+            assert np.array_equal(b.read_rgba8(), o["rgba"]) and rays == o["rays"], (w, h)
+        # strided SUM shards (the multi-GPU path) chunked the same way
+        w, h, n = 40, 30, 10
+        cam = srt.host_camera(2, w, h, hdr)
+        b.set_scene(spheres, sky, 8, True)
+        b.resize(w, h)
+        o_acc = np.zeros((h, w, 4), np.float32)
+        for shard in range(2):
+            b.render(cam, shard, n // 2, stride=2, mode=1)
+            b.wait()
+            o_acc, _ = oracle.render_sum(spheres, sky, 8, 1, cam, w, h, shard, n // 2, 2, accum=o_acc)
+            assert np.array_equal(b.read_accum()[..., :3].view(np.uint32), o_acc[..., :3].view(np.uint32))
+    finally:
+        b.close()
