@@ -1013,7 +1013,17 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad, pc.threads) <= b->max_smem_optin;
     // kernel choice: tiny scenes -> one path per thread; otherwise the pool kernel, with the sphere
     // tables resident in shared memory when they fit and streamed through per-warp TMA stages when not
-    const bool pool_res_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, kPoolThreads, false) <= b->max_smem_optin;
+    // experiment (SRT_POOL_THREADS, W=8 FMA resident only): one big CTA per SM instead of two of 256 threads
+    int pool_threads = kPoolThreads;
+    if (const char *v = getenv("SRT_POOL_THREADS")) {
+        const int t = atoi(v);
+        if ((t == 512 || t == 640 || t == 768) && b->opt.lane_width == 8 && b->opt.fma_dot && b->variant != 12) pool_threads = t;
+    }
+    bool pool_res_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, pool_threads, false) <= b->max_smem_optin;
+    if (!pool_res_fit && pool_threads != kPoolThreads) {
+        pool_threads = kPoolThreads;
+        pool_res_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, pool_threads, false) <= b->max_smem_optin;
+    }
     const bool want_pool = b->variant == 9 || b->variant == 12 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres);
     const bool pool = want_pool;
     const bool stream = pool && (b->variant == 12 || !pool_res_fit);
@@ -1053,8 +1063,12 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
             SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
     }
     render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, b->n_pad, stream) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
-    const int threads = pool ? kPoolThreads : pairs ? pc.threads : kBlockThreads;
-    const size_t smem = pool ? pool_smem_bytes(b->n_pad, kPoolThreads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
+    if (stream) pool_threads = kPoolThreads;
+    if (pool && pool_threads == 512) kernel = render_pool<8, true, 512, 1, 32, 32, false>;
+    if (pool && pool_threads == 640) kernel = render_pool<8, true, 640, 1, 32, 32, false>;
+    if (pool && pool_threads == 768) kernel = render_pool<8, true, 768, 1, 32, 32, false>;
+    const int threads = pool ? pool_threads : pairs ? pc.threads : kBlockThreads;
+    const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
