@@ -160,7 +160,7 @@ def run_reference_arm(args):
         "e2e": {"value": r["mrays"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": wall,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_STDOUT, flush=True)
     return 0
 
 
@@ -389,10 +389,13 @@ def run_gpu_arm(args):
         line["cpu_baseline"] = cpu
     if lat is not None:
         line["frame_latency_1080p"] = lat
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_STDOUT, flush=True)
     if dist is not None:
         dist.destroy_process_group()
     return 0
+
+
+_STDOUT = sys.stdout
 
 
 def main():
@@ -407,6 +410,12 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
     args = ap.parse_args()
+    # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version
+    # banner there) are sent to stderr while the benchmark runs.
+    global _STDOUT
+    sys.stdout.flush()
+    _STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_gpu_arm(args)
