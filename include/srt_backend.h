@@ -114,13 +114,14 @@ int srt_poll(srt_backend *b);
  * batch (CUDA events), out_rays = path segments cast by it, counted like main.cpp:390. */
 int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays);
 
-/* Diagnostic: soundness audit of the ray-pair kernel's conservative sphere filter
- * (csrc/srt_pairs.cuh).  Traces the same paths as srt_render(first_sample, n_samples) would,
+/* Diagnostic: soundness audit of the ray-pair kernel's conservative sphere filters
+ * (csrc/srt_pairs.cuh: level 1 slab test, level 2 fused 7-FMA test).  Traces the same paths as srt_render(first_sample, n_samples) would,
  * with the reference's per-lane arithmetic, and for EVERY (path segment, sphere) pair evaluates
  * both the reference's hit predicate (main.cpp:409 / :557) and the filter predicate.  Blocking.
- * out_counts = { tests, exact hits, filter candidates, violations }; the filter is sound iff
- * violations (an exact hit the filter would have dropped) is 0.  Touches no image buffer. */
-int srt_filter_audit(srt_backend *b, const srt_camera *camera, const srt_render_args *args, uint64_t out_counts[4]);
+ * out_counts = { tests, exact hits, candidates (pass both levels), violations, level-1 survivors };
+ * the filters are sound iff violations (an exact hit either level would have dropped) is 0.
+ * Touches no image buffer. */
+int srt_filter_audit(srt_backend *b, const srt_camera *camera, const srt_render_args *args, uint64_t out_counts[5]);
 
 /* accum holds a SUM over `total_samples`: mean = sum * (1/N), tonemap + pack into rgba
  * (main.cpp:312-346). Asynchronous on the backend stream; ordered after prior renders. */

@@ -149,12 +149,12 @@ class Backend:
         return ms.value, rays.value
 
     def filter_audit(self, camera, first_sample=0, n_samples=1, stream_base=0):
-        """Soundness audit of the ray-pair kernel's sphere filter: dict(tests, hits, candidates, violations)."""
+        """Soundness audit of the sphere filters: dict(tests, hits, candidates, violations, slab_survivors)."""
         cam = np.ascontiguousarray(camera)
         args = RenderArgs(first_sample, n_samples, 1, ACCUM_MEAN, stream_base, 0, 0)
-        counts = (C.c_uint64 * 4)()
+        counts = (C.c_uint64 * 5)()
         self._check(self.L.srt_filter_audit(self.h, cam.ctypes.data, C.byref(args), counts))
-        return dict(tests=counts[0], hits=counts[1], candidates=counts[2], violations=counts[3])
+        return dict(tests=counts[0], hits=counts[1], candidates=counts[2], violations=counts[3], slab_survivors=counts[4])
 
     def resolve_sum(self, total_samples):
         self._check(self.L.srt_resolve_sum(self.h, total_samples))

@@ -12,6 +12,7 @@
 #include "srt_pool.cuh"
 #include "srt_stream.cuh"
 
+#include <algorithm>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -291,45 +292,54 @@ __device__ __forceinline__ float ptab_value(float4 c, float r2, double ox, doubl
     const double oo = (ox * ox + oy * oy + oz * oz) * (1.0 - 160.0 * u);
     return (float)(2.0 * (cx * ox + cy * oy + cz * oz) - (c2 - R) - oo);
 }
-// Streamed scenes: the primary table is built once per launch in global memory.
-__global__ void build_ptab_kernel(const float4 *scan, const float4 *spheres, float4 *ptab, uint32_t n_pad, uint32_t n_real,
-                                  float ox, float oy, float oz) {
+// Slab table entry of sphere i (srt_pairs.cuh): kept-axis coordinates and the inflated radius.
+__device__ __forceinline__ void slab_entry(float *table, uint32_t i, float4 c, float r2, bool real, int axis, float omax) {
+    const float cp = axis == 0 ? c.y : (axis == 1 ? c.z : c.x), cq = axis == 0 ? c.z : (axis == 1 ? c.x : c.y);
+    float *g = table + (i >> 2) * 12u + (i & 3u);
+    g[0] = cp; g[4] = cq; g[8] = real ? slab_radius(r2, c.x, c.y, c.z, omax) : -1.0f;
+}
+// Streamed scenes: the slab table is built once per launch in global memory.
+__global__ void build_slab_kernel(const float4 *scan, const float4 *spheres, float *table, uint32_t n_pad, uint32_t n_real, int axis, float omax) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pad) return;
-    const float4 c = scan[i];
-    ptab[i] = make_float4(c.x, c.y, c.z, i < n_real ? ptab_value(c, spheres[i].w, ox, oy, oz) : -1.0e30f);
+    slab_entry(table, i, scan[i], spheres[i].w, i < n_real, axis, omax);
 }
 
-// One pass of a warp over a streamed table (srt_stream.cuh): TMA bulk copies into the warp's
-// ring of stages, scan of each chunk, select after every kPairsMaxSpheres spheres.
-template <int SUB, int W, bool FMA, class Rays>
-__device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__restrict__ table, const float4 *__restrict__ spheres,
-                                            uint32_t n_pad, uint32_t n_real, const Rays &rays, unsigned lane,
+// One pass of a warp over the streamed slab table (srt_stream.cuh): TMA bulk copies into the
+// warp's ring of stages, level-1 scan of each chunk; refine (level 2) + select after every
+// kPairsMaxSpheres spheres against the {c,-kappa} and {c,r2} tables in global memory (L2).
+template <int W, bool FMA>
+__device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__restrict__ slab, const float4 *__restrict__ scan,
+                                            const float4 *__restrict__ spheres, uint32_t n_pad, uint32_t n_real,
+                                            const SlabRays &sr, const ScanRays &rays, unsigned lane,
                                             pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, float neg_one, float one, Best &b0, Best &b1) {
+    constexpr uint32_t kF4 = kStreamChunk * 3 / 4;            // float4 per chunk of the slab table
     const uint32_t n_chunks = (n_pad + kStreamChunk - 1) / kStreamChunk;
     if (lane == 0) {
         for (uint32_t c = 0; c < (uint32_t)kStreamStages && c < n_chunks; ++c) {
             const uint32_t cnt = min((uint32_t)kStreamChunk, n_pad - c * kStreamChunk);
-            stream_issue(ws.stage + c * kStreamChunk, table + c * kStreamChunk, cnt * (uint32_t)sizeof(float4), ws.bar + c);
+            stream_issue(ws.stage + c * kStreamChunk, slab + c * kF4, cnt * 12u, ws.bar + c);
         }
     }
     CandQueue queue;
     uint32_t qn = 0;
     const FetchGlobal fetch = {spheres};
+    const FetchScanGlobal fetch_scan = {scan};
 #pragma unroll 1
     for (uint32_t c = 0; c < n_chunks; ++c) {
         const uint32_t st = c % kStreamStages;
         mbar_wait(ws.bar + st, (ws.parity >> st) & 1u);
         ws.parity ^= 1u << st;
         const uint32_t cnt = min((uint32_t)kStreamChunk, n_pad - c * kStreamChunk);
-        scan_tile<SUB>(ws.stage + st * kStreamChunk, cnt, c * kStreamChunk, rays, queue, qn);
+        scan_slab_tile(ws.stage + st * kStreamChunk, cnt, c * kStreamChunk, sr, queue, qn);
         __syncwarp();
         const uint32_t nc = c + kStreamStages;
         if (lane == 0 && nc < n_chunks) {
             const uint32_t ncnt = min((uint32_t)kStreamChunk, n_pad - nc * kStreamChunk);
-            stream_issue(ws.stage + st * kStreamChunk, table + nc * kStreamChunk, ncnt * (uint32_t)sizeof(float4), ws.bar + st);
+            stream_issue(ws.stage + st * kStreamChunk, slab + nc * kF4, ncnt * 12u, ws.bar + st);
         }
         if (((c + 1) * kStreamChunk) % kPairsMaxSpheres == 0 || c + 1 == n_chunks) {
+            refine_queue(fetch_scan, queue, qn, rays);
             select_update<W, FMA>(fetch, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one, one, b0, b1);
             qn = 0;
         }
@@ -343,8 +353,8 @@ render_pool(const __grid_constant__ KernelParams P) {
     constexpr uint32_t RCAP = NS <= 1024u ? 1024u : 2048u;     // ring capacity (power of two >= NS)
     extern __shared__ float4 s_scan[];                         // resident: {cx,cy,cz,-kappa}
     const uint32_t n_res = STREAM ? 0u : P.n_pad;              // spheres resident in shared memory
-    float4 *const s_ptab = s_scan + n_res;                     // resident: {cx,cy,cz, 2C.O - kappa - oo'} for the camera origin
-    float *const s_r2 = reinterpret_cast<float *>(s_ptab + n_res);
+    float4 *const s_slab = s_scan + n_res;                     // resident: slab table, 3 float4 per 4 spheres (srt_pairs.cuh)
+    float *const s_r2 = reinterpret_cast<float *>(s_slab + (n_res >> 2) * 3u);
     float *const st = s_r2 + n_res;
     uint32_t *const su = reinterpret_cast<uint32_t *>(st);
     uint32_t *const ring0 = su + S_COUNT * NS;
@@ -371,7 +381,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                 const float r2 = P.spheres[i].w;
                 s_scan[i] = c;
                 s_r2[i] = r2;
-                s_ptab[i] = make_float4(c.x, c.y, c.z, i < P.n_spheres ? ptab_value(c, r2, cam_o.x, cam_o.y, cam_o.z) : -1.0e30f);
+                slab_entry(reinterpret_cast<float *>(s_slab), i, c, r2, i < P.n_spheres, P.slab_axis, P.omax);
             }
         } else if (lane == 0) {
             for (int i = 0; i < kStreamStages; ++i) mbar_init(ws.bar + i, 1u);
@@ -478,7 +488,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                 }
                 const unsigned rm = __ballot_sync(0xFFFFFFFFu, retire);
                 if (rm && lane == (unsigned)(__ffs(rm) - 1)) atomicAdd(&ctl->retired, (unsigned)__popc(rm));
-                f3 o = cam_o, d = mk3(0.0f, 0.0f, 0.0f);
+                f3 o = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin), d = mk3(0.0f, 0.0f, 0.0f);   // parked unless a ray is generated
                 if (retire) { SRT_SU(S_PIX, s) = kInvalidPixel; if (r) id1 = kRingEmpty; else id0 = kRingEmpty; }
                 else if (valid && pending) {
                     SRT_SU(S_PIX, s) = pix; SRT_SU(S_K, s) = k; SRT_SU(S_KEND, s) = kend; SRT_SU(S_PXY, s) = pxy; SRT_SU(S_FLAGS, s) = kFlagPending;
@@ -495,16 +505,6 @@ render_pool(const __grid_constant__ KernelParams P) {
                 if (r) { o1 = o; d1 = d; } else { o0 = o; d0 = d; }
             }
             any_real = __any_sync(0xFFFFFFFFu, real);
-            ox = pk_make(cam_o.x, cam_o.x); oy = pk_make(cam_o.y, cam_o.y); oz = pk_make(cam_o.z, cam_o.z);
-            dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
-            const ScanPrimary rays_p = make_scan_primary(cam_o.x, cam_o.y, cam_o.z, dx, dy, dz);
-            if (!any_real) {
-                // nothing runnable in this batch (slots waiting for a chunk, or retiring)
-            } else if (STREAM) {
-                stream_pass<SUBP, W, FMA>(ws, P.ptab, P.spheres, P.n_pad, P.n_spheres, rays_p, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
-            } else {
-                scan_primary_tile<SUBP>(s_ptab, P.n_pad, 0u, rays_p, queue, qn);
-            }
         } else {
             // ---- 64 slots with a secondary ray ready ------------------------------------------
             o0 = o1 = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin);
@@ -517,17 +517,20 @@ render_pool(const __grid_constant__ KernelParams P) {
                 o1 = mk3(SRT_ST(S_OX, id1), SRT_ST(S_OY, id1), SRT_ST(S_OZ, id1));
                 d1 = mk3(SRT_ST(S_DX, id1), SRT_ST(S_DY, id1), SRT_ST(S_DZ, id1));
             }
-            ox = pk_make(o0.x, o1.x); oy = pk_make(o0.y, o1.y); oz = pk_make(o0.z, o1.z);
-            dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
-            const ScanRays rays_s = make_scan_rays(ox, oy, oz, dx, dy, dz);
-            if (STREAM) {
-                stream_pass<SUB, W, FMA>(ws, P.scan_table, P.spheres, P.n_pad, P.n_spheres, rays_s, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
-            } else {
-                scan_general_tile<SUB>(s_scan, P.n_pad, 0u, rays_s, queue, qn);
-            }
         }
+        ox = pk_make(o0.x, o1.x); oy = pk_make(o0.y, o1.y); oz = pk_make(o0.z, o1.z);
+        dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
         if (any_real) {
-            if (!STREAM) {
+            // level 1 (slab, every sphere) -> level 2 (7-FMA filter on the survivors) -> exact select
+            const SlabRays sr = make_slab_rays(P.slab_axis, ox, oy, oz, dx, dy, dz, P.omax2);
+            if (STREAM) {
+                const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
+                stream_pass<W, FMA>(ws, P.ptab, P.scan_table, P.spheres, P.n_pad, P.n_spheres, sr, rays, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+            } else {
+                scan_slab_tile(s_slab, P.n_pad, 0u, sr, queue, qn);
+                const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
+                const FetchScanResident fetch_scan = {s_scan};
+                refine_queue(fetch_scan, queue, qn, rays);
                 const FetchResident fetch = {s_scan, s_r2};
                 select_update<W, FMA>(fetch, P.n_spheres, queue, qn, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
             }
@@ -598,7 +601,7 @@ render_pool(const __grid_constant__ KernelParams P) {
 template <int W, bool FMA>
 __global__ void __launch_bounds__(kBlockThreads)
 audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counters) {
-    unsigned long long n_tests = 0, n_hits = 0, n_cand = 0, n_viol = 0;
+    unsigned long long n_tests = 0, n_hits = 0, n_cand = 0, n_viol = 0, n_slab = 0;
     const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
     if (pix < P.width * P.height) {
         const uint32_t px = pix % P.width, py = pix / P.width;
@@ -611,8 +614,11 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
                 const FilterRay f = filter_ray(o.x, o.y, o.z, d.x, d.y, d.z);
                 const pk2 p2ox = pk_make(f.p2ox, f.p2ox), p2oy = pk_make(f.p2oy, f.p2oy), p2oz = pk_make(f.p2oz, f.p2oz);
                 const pk2 fdx = pk_make(f.dx, f.dx), fdy = pk_make(f.dy, f.dy), fdz = pk_make(f.dz, f.dz), od = pk_make(f.od, f.od);
+                const SlabRay sl = slab_ray(P.slab_axis, o.x, o.y, o.z, d.x, d.y, d.z, P.omax2);
                 for (uint32_t i = 0; i < P.n_pad; ++i) {
                     const float4 s = P.spheres[i];
+                    const float cp = P.slab_axis == 0 ? s.y : (P.slab_axis == 1 ? s.z : s.x), cq = P.slab_axis == 0 ? s.z : (P.slab_axis == 1 ? s.x : s.y);
+                    const bool slab = slab_test(cp, cq, i < P.n_spheres ? slab_radius(s.w, s.x, s.y, s.z, P.omax) : -1.0f, sl);
                     const float scx = __fsub_rn(s.x, o.x), scy = __fsub_rn(s.y, o.y), scz = __fsub_rn(s.z, o.z);
                     const float t = lane_dot<(W != 1) && FMA>(scx, scy, scz, d.x, d.y, d.z);
                     const float vx = __fsub_rn(scx, __fmul_rn(d.x, t));
@@ -624,8 +630,9 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
                     filter_sphere(mask, 1u, P.scan_table[i], p2ox, p2oy, p2oz, fdx, fdy, fdz, od, f.oo, f.oo);
                     n_tests += 1;
                     n_hits += exact ? 1 : 0;
-                    n_cand += mask;
-                    n_viol += (exact && !mask) ? 1 : 0;
+                    n_slab += slab ? 1 : 0;
+                    n_cand += (slab && mask) ? 1 : 0;
+                    n_viol += (exact && !(slab && mask)) ? 1 : 0;
                 }
                 Hit h;
                 if (W == 1) h = intersect_scalar(P.spheres, P.n_pad, P.n_spheres, o, d);
@@ -641,12 +648,14 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
         n_hits += __shfl_down_sync(0xFFFFFFFFu, n_hits, off);
         n_cand += __shfl_down_sync(0xFFFFFFFFu, n_cand, off);
         n_viol += __shfl_down_sync(0xFFFFFFFFu, n_viol, off);
+        n_slab += __shfl_down_sync(0xFFFFFFFFu, n_slab, off);
     }
     if ((threadIdx.x & 31u) == 0) {
         atomicAdd(&counters[0], n_tests);
         atomicAdd(&counters[1], n_hits);
         atomicAdd(&counters[2], n_cand);
         atomicAdd(&counters[3], n_viol);
+        atomicAdd(&counters[4], n_slab);
     }
 }
 
@@ -696,6 +705,8 @@ struct srt_backend {
     // counters: [0..7] rays (u64), [8..11] work counter
     unsigned char *d_counters = nullptr;
     uint32_t *d_done = nullptr;          // pool kernel: per-pixel chunk counters (KernelParams::done)
+    int slab_axis = 1;                   // axis contained in the slab planes: least spread of the centres
+    double omax_scene = 0.0;             // >= |C| + r of every sphere (bound on secondary-ray origins)
     uint32_t pool_chunk = 0;             // samples per work item, 0 = kPoolChunkSamples (SRT_POOL_CHUNK)
     unsigned long long *h_rays = nullptr;   // pinned
     bool in_flight = false;
@@ -769,7 +780,7 @@ static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
     const size_t ns = 64u * (threads / 32 + 2), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
     size_t bytes = (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
     if (stream) bytes += warps * kStreamStages * (kStreamChunk * sizeof(float4) + sizeof(uint64_t));
-    else bytes += (size_t)n_pad * (2 * sizeof(float4) + sizeof(float));
+    else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
     return bytes;
 }
 static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
@@ -875,6 +886,35 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
         const double c2 = cx * cx + cy * cy + cz * cz;
         const double R = r2 * (1.0 + 128.0 * u) + 128.0 * u * c2 + 1.0e-30;
         scan[i] = make_float4(sph[i].x, sph[i].y, sph[i].z, (float)(R - c2));
+    }
+    // Slab filter (srt_pairs.cuh): the slab planes contain the coordinate axis along which the centres
+    // spread least (ignoring spheres much larger than the median one, e.g. a ground sphere); Omax bounds
+    // the origins of secondary rays, which lie on sphere surfaces.
+    {
+        std::vector<double> radii(n_spheres);
+        for (uint32_t i = 0; i < n_spheres; ++i) radii[i] = sqrt((double)sph[i].w);
+        std::vector<double> sorted = radii;
+        std::nth_element(sorted.begin(), sorted.begin() + n_spheres / 2, sorted.end());
+        const double cutoff = 10.0 * sorted[n_spheres / 2];
+        double sum[3] = {0, 0, 0}, sq[3] = {0, 0, 0}, cnt = 0, omax = 0;
+        for (uint32_t i = 0; i < n_spheres; ++i) {
+            const double c[3] = {sph[i].x, sph[i].y, sph[i].z};
+            omax = std::max(omax, sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]) + radii[i]);
+            if (radii[i] > cutoff) continue;
+            for (int a = 0; a < 3; ++a) { sum[a] += c[a]; sq[a] += c[a] * c[a]; }
+            cnt += 1;
+        }
+        int axis = 1;
+        if (cnt >= 2) {
+            double best = 0;
+            for (int a = 0; a < 3; ++a) {
+                const double var = sq[a] / cnt - (sum[a] / cnt) * (sum[a] / cnt);
+                if (a == 0 || var < best) { best = var; axis = a; }
+            }
+        }
+        b->slab_axis = axis;
+        if (const char *v = getenv("SRT_SLAB_AXIS")) b->slab_axis = std::min(2, std::max(0, atoi(v)));
+        b->omax_scene = omax * 1.01 + 1e-3;
     }
     cudaFree(b->d_spheres); b->d_spheres = nullptr;
     cudaFree(b->d_scan); b->d_scan = nullptr;
@@ -997,6 +1037,12 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.debug = (unsigned long long *)(b->d_counters + 16);
     P.items_per_gen = P.total_items;
     P.chunk_span = 0;
+    // slab filter (srt_pairs.cuh): bound on the ray origins of this launch = the scene's bound or the camera
+    const double cam_len = sqrt((double)cam->camera_position[0] * cam->camera_position[0] + (double)cam->camera_position[1] * cam->camera_position[1] +
+                                (double)cam->camera_position[2] * cam->camera_position[2]);
+    P.slab_axis = b->slab_axis;
+    P.omax = (float)(std::max(b->omax_scene, cam_len * 1.001 + 1e-3) * 1.0001);
+    P.omax2 = P.omax * P.omax;
     return SRT_OK;
 }
 
@@ -1082,8 +1128,8 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
     if (stream) {
         P.ptab = b->d_ptab;
-        build_ptab_kernel<<<(b->n_pad + 255) / 256, 256, 0, b->stream>>>(b->d_scan, b->d_spheres, b->d_ptab, b->n_pad, b->n_spheres,
-                                                                        P.cam.pos[0], P.cam.pos[1], P.cam.pos[2]);
+        build_slab_kernel<<<(b->n_pad + 255) / 256, 256, 0, b->stream>>>(b->d_scan, b->d_spheres, (float *)b->d_ptab, b->n_pad, b->n_spheres,
+                                                                        P.slab_axis, P.omax);
         b->launches += 1;
     }
     kernel<<<grid, threads, smem, b->stream>>>(P);
@@ -1124,7 +1170,7 @@ int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays) {
     return SRT_OK;
 }
 
-int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_args *args, uint64_t out_counts[4]) {
+int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_args *args, uint64_t out_counts[5]) {
     if (!b) return SRT_ERR_INVALID;
     if (!out_counts) return fail(b, SRT_ERR_INVALID, "srt_filter_audit: null output");
     KernelParams P;
@@ -1135,8 +1181,8 @@ int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_arg
     rc = drain(b);
     if (rc) return rc;
     unsigned long long *d_cnt = nullptr;
-    SRT_CUDA(b, cudaMalloc(&d_cnt, 4 * sizeof(unsigned long long)));
-    SRT_CUDA(b, cudaMemsetAsync(d_cnt, 0, 4 * sizeof(unsigned long long), b->stream));
+    SRT_CUDA(b, cudaMalloc(&d_cnt, 8 * sizeof(unsigned long long)));
+    SRT_CUDA(b, cudaMemsetAsync(d_cnt, 0, 8 * sizeof(unsigned long long), b->stream));
     const uint32_t n = b->width * b->height;
     const dim3 grid((n + kBlockThreads - 1) / kBlockThreads);
     const srt_scene_options &o = b->opt;
@@ -1146,12 +1192,12 @@ int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_arg
     else if (o.fma_dot) audit_filter<8, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     else audit_filter<8, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     cudaError_t e = cudaGetLastError();
-    unsigned long long h[4] = {0, 0, 0, 0};
+    unsigned long long h[5] = {0, 0, 0, 0, 0};
     if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, b->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
     cudaFree(d_cnt);
     if (e != cudaSuccess) return fail(b, SRT_ERR_CUDA, std::string("srt_filter_audit: ") + cudaGetErrorString(e));
-    for (int i = 0; i < 4; ++i) out_counts[i] = h[i];
+    for (int i = 0; i < 5; ++i) out_counts[i] = h[i];
     b->launches += 1;
     return SRT_OK;
 }

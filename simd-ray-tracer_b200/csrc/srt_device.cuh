@@ -119,7 +119,9 @@ struct KernelParams {
     const float4 *spheres;       // n_pad entries {cx,cy,cz,r2}, zero spheres as padding (never hit);
                                  // packed kernels: pair layout {x0,x1,y0,y1},{z0,z1,r2_0,r2_1}
     const float4 *scan_table;    // pair kernel: n_pad entries {cx,cy,cz,-kappa} (srt_pairs.cuh), padding -1e30
-    const float4 *ptab;          // streamed scenes: n_pad entries {cx,cy,cz, primary-ray filter constant}, built per launch
+    const float4 *ptab;          // streamed scenes: the launch's slab table (3 float4 per 4 spheres, srt_pairs.cuh), built per launch
+    int32_t slab_axis;           // coordinate axis the slab planes contain (0/1/2), chosen at scene upload
+    float omax, omax2;           // bound on |ray origin| the slab radii were inflated for, and its square
     const DevMaterial *materials;
     uint32_t n_pad;              // multiple of 8
     uint32_t n_spheres;          // real sphere count
