@@ -142,6 +142,10 @@ render_paths(const __grid_constant__ KernelParams P) {
 // ------------------------------------------------------------------------------------------
 enum : int { S_OX, S_OY, S_OZ, S_DX, S_DY, S_DZ, S_AX, S_AY, S_AZ, S_LX, S_LY, S_LZ, S_MX, S_MY, S_MZ,
              S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_KEND, S_COUNT };
+#ifndef SRT_POOL_SPARE
+#define SRT_POOL_SPARE 2
+#endif
+constexpr uint32_t kPoolSpareBatches = SRT_POOL_SPARE;   // path slots per CTA = 64 x (warps + spare)
 constexpr uint32_t kFlagBounceMask = 7u, kFlagActive = 8u, kFlagDone = 16u, kFlagPending = 32u;
 
 template <int W, bool FMA, int THREADS, int MINB>
@@ -282,16 +286,6 @@ render_pairs(const __grid_constant__ KernelParams P) {
 // render_pool: render_pairs with the path slots owned by the CTA (srt_pool.cuh).  A warp pass
 // is either 64 PRIMARY rays (regenerate + 4-FFMA2 filter) or 64 SECONDARY rays (7-FFMA2 filter).
 // ------------------------------------------------------------------------------------------
-// ptab_value: the primary-ray filter constant of one sphere, in double, rounded once:
-// 2 C.O - kappa - oo' = -(|C-O|^2 - R) - |O|^2 (1 - 160u)   (srt_pairs.cuh)
-__device__ __forceinline__ float ptab_value(float4 c, float r2, double ox, double oy, double oz) {
-    const double u = 5.9604644775390625e-08;
-    const double cx = c.x, cy = c.y, cz = c.z;
-    const double c2 = cx * cx + cy * cy + cz * cz;
-    const double R = (double)r2 * (1.0 + 128.0 * u) + 128.0 * u * c2 + 1.0e-30;
-    const double oo = (ox * ox + oy * oy + oz * oz) * (1.0 - 160.0 * u);
-    return (float)(2.0 * (cx * ox + cy * oy + cz * oz) - (c2 - R) - oo);
-}
 // Slab table entry of sphere i (srt_pairs.cuh): kept-axis coordinates and the inflated radius.
 __device__ __forceinline__ void slab_entry(float *table, uint32_t i, float4 c, float r2, bool real, int axis, float omax) {
     const float cp = axis == 0 ? c.y : (axis == 1 ? c.z : c.x), cq = axis == 0 ? c.z : (axis == 1 ? c.x : c.y);
@@ -346,10 +340,10 @@ __device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__rest
     }
 }
 
-template <int W, bool FMA, int THREADS, int MINB, int SUB, int SUBP, bool STREAM>
+template <int W, bool FMA, int THREADS, int MINB, bool STREAM>
 __global__ void __launch_bounds__(THREADS, MINB)
 render_pool(const __grid_constant__ KernelParams P) {
-    constexpr uint32_t NS = 64u * (THREADS / 32 + 2);          // slots per CTA
+    constexpr uint32_t NS = 64u * (THREADS / 32 + kPoolSpareBatches);   // slots per CTA
     constexpr uint32_t RCAP = NS <= 1024u ? 1024u : 2048u;     // ring capacity (power of two >= NS)
     extern __shared__ float4 s_scan[];                         // resident: {cx,cy,cz,-kappa}
     const uint32_t n_res = STREAM ? 0u : P.n_pad;              // spheres resident in shared memory
@@ -760,24 +754,28 @@ static PairConfig pick_pairs_kernel(const srt_scene_options &o) {
     return {kPairThreads, o.fma_dot ? render_pairs<8, true, kPairThreads, kPairMinBlocks> : render_pairs<8, false, kPairThreads, kPairMinBlocks>};
 }
 // Pool kernel (srt_pool.cuh): CTA-owned path slots, primary / secondary warp passes.
-constexpr int kPoolThreads = 256;
+// Pool kernel configurations.  Resident tables: one large CTA per SM -- the refine / select / shade
+// phases of a pass are latency-bound, the slab scan is issue-bound, and only warps in the scan keep
+// the issue port busy: 28 warps (72 registers) beat 16 warps (2 x 256 threads) by 24 % on the
+// 1,024-sphere scene.  Larger scenes trade warps for table space; beyond that the tables are streamed.
+constexpr int kPoolThreads = 256;           // streamed kernel: 2 CTAs of 256 threads
 constexpr int kPoolMinBlocks = 2;
 constexpr uint32_t kPoolChunkSamples = 1;   // samples per pool work item (measured best: 1; SRT_POOL_CHUNK overrides)
-// Unroll of the secondary-ray scan: 32 spheres per loop body is 3 % faster on >= 768 spheres, 16
-// is 4-9 % faster below (the bodies share the 6 KB L0 / 32 KB L1.5 instruction caches with the
-// primary scan, select and shade code).  Measured on B200, profiles/r1d_pool_tuning.log.
-template <int SUB, bool STREAM>
-static render_kernel_t pick_pool_kernel_sub(const srt_scene_options &o) {
-    if (o.lane_width == 1) return render_pool<1, false, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM>;
-    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM> : render_pool<4, false, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM>;
-    return o.fma_dot ? render_pool<8, true, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM> : render_pool<8, false, kPoolThreads, kPoolMinBlocks, SUB, 32, STREAM>;
+constexpr int kPoolResidentThreads[3] = {896, 512, 256};
+template <int THREADS, int MINB, bool STREAM>
+static render_kernel_t pick_pool_kernel_cfg(const srt_scene_options &o) {
+    if (o.lane_width == 1) return render_pool<1, false, THREADS, MINB, STREAM>;
+    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, THREADS, MINB, STREAM> : render_pool<4, false, THREADS, MINB, STREAM>;
+    return o.fma_dot ? render_pool<8, true, THREADS, MINB, STREAM> : render_pool<8, false, THREADS, MINB, STREAM>;
 }
-static render_kernel_t pick_pool_kernel(const srt_scene_options &o, uint32_t n_pad, bool stream) {
-    if (stream) return pick_pool_kernel_sub<32, true>(o);
-    return n_pad >= 768 ? pick_pool_kernel_sub<32, false>(o) : pick_pool_kernel_sub<16, false>(o);
+static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream, int threads) {
+    if (stream) return pick_pool_kernel_cfg<kPoolThreads, kPoolMinBlocks, true>(o);
+    if (threads == 896) return pick_pool_kernel_cfg<896, 1, false>(o);
+    if (threads == 512) return pick_pool_kernel_cfg<512, 1, false>(o);
+    return pick_pool_kernel_cfg<256, 1, false>(o);
 }
 static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
-    const size_t ns = 64u * (threads / 32 + 2), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
+    const size_t ns = 64u * (threads / 32 + kPoolSpareBatches), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
     size_t bytes = (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
     if (stream) bytes += warps * kStreamStages * (kStreamChunk * sizeof(float4) + sizeof(uint64_t));
     else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
@@ -1059,17 +1057,13 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad, pc.threads) <= b->max_smem_optin;
     // kernel choice: tiny scenes -> one path per thread; otherwise the pool kernel, with the sphere
     // tables resident in shared memory when they fit and streamed through per-warp TMA stages when not
-    // experiment (SRT_POOL_THREADS, W=8 FMA resident only): one big CTA per SM instead of two of 256 threads
-    int pool_threads = kPoolThreads;
-    if (const char *v = getenv("SRT_POOL_THREADS")) {
-        const int t = atoi(v);
-        if ((t == 512 || t == 640 || t == 768) && b->opt.lane_width == 8 && b->opt.fma_dot && b->variant != 12) pool_threads = t;
+    // resident configuration with the most warps whose tables + path slots fit in shared memory
+    int pool_threads = 0;
+    for (int t : kPoolResidentThreads) {
+        if (const char *v = getenv("SRT_POOL_THREADS")) { if (atoi(v) != t) continue; }
+        if (b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, t, false) <= b->max_smem_optin) { pool_threads = t; break; }
     }
-    bool pool_res_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, pool_threads, false) <= b->max_smem_optin;
-    if (!pool_res_fit && pool_threads != kPoolThreads) {
-        pool_threads = kPoolThreads;
-        pool_res_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, pool_threads, false) <= b->max_smem_optin;
-    }
+    const bool pool_res_fit = pool_threads != 0;
     const bool want_pool = b->variant == 9 || b->variant == 12 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres);
     const bool pool = want_pool;
     const bool stream = pool && (b->variant == 12 || !pool_res_fit);
@@ -1108,19 +1102,21 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         if (P.done_tag == 0u && n_chunks > 1u)   // sequence wrapped: forget counts of 2^20 launches ago
             SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
     }
-    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, b->n_pad, stream) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
-    if (stream) pool_threads = kPoolThreads;
-    if (pool && pool_threads == 512) kernel = render_pool<8, true, 512, 1, 32, 32, false>;
-    if (pool && pool_threads == 640) kernel = render_pool<8, true, 640, 1, 32, 32, false>;
-    if (pool && pool_threads == 768) kernel = render_pool<8, true, 768, 1, 32, 32, false>;
+    if (stream || !pool_res_fit) pool_threads = kPoolThreads;
+    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
     const int threads = pool ? pool_threads : pairs ? pc.threads : kBlockThreads;
     const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (pool) {   // leave the rest of the 256 KB to L1: the candidate queues live in local memory
+        const size_t ctas = stream ? kPoolMinBlocks : 1;
+        const int carve = (int)std::min<size_t>(100, (ctas * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+        SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+    }
     int per_sm = 0;
     SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
     if (per_sm < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
     uint32_t grid = (uint32_t)(b->sm_count * per_sm);                 // persistent: one resident wave
-    const uint32_t paths_per_block = pool ? 64u * (threads / 32 + 2) : (uint32_t)threads * (pairs ? 2u : 1u);
+    const uint32_t paths_per_block = pool ? 64u * (threads / 32 + kPoolSpareBatches) : (uint32_t)threads * (pairs ? 2u : 1u);
     const uint32_t max_useful = (P.total_items + paths_per_block - 1) / paths_per_block;
     if (grid > max_useful) grid = max_useful;
 
