@@ -307,12 +307,12 @@ __device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__rest
                                             const float4 *__restrict__ spheres, uint32_t n_pad, uint32_t n_real,
                                             const SlabRays &sr, const ScanRays &rays, unsigned lane,
                                             pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, float neg_one, float one, Best &b0, Best &b1) {
-    constexpr uint32_t kF4 = kStreamChunk * 3 / 4;            // float4 per chunk of the slab table
+    constexpr uint32_t kF4 = kStreamStageF4;                  // float4 per chunk of the slab table
     const uint32_t n_chunks = (n_pad + kStreamChunk - 1) / kStreamChunk;
     if (lane == 0) {
         for (uint32_t c = 0; c < (uint32_t)kStreamStages && c < n_chunks; ++c) {
             const uint32_t cnt = min((uint32_t)kStreamChunk, n_pad - c * kStreamChunk);
-            stream_issue(ws.stage + c * kStreamChunk, slab + c * kF4, cnt * 12u, ws.bar + c);
+            stream_issue(ws.stage + c * kF4, slab + c * kF4, cnt * 12u, ws.bar + c);
         }
     }
     CandQueue queue;
@@ -325,12 +325,12 @@ __device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__rest
         mbar_wait(ws.bar + st, (ws.parity >> st) & 1u);
         ws.parity ^= 1u << st;
         const uint32_t cnt = min((uint32_t)kStreamChunk, n_pad - c * kStreamChunk);
-        scan_slab_tile(ws.stage + st * kStreamChunk, cnt, c * kStreamChunk, sr, queue, qn);
+        scan_slab_tile(ws.stage + st * kF4, cnt, c * kStreamChunk, sr, queue, qn);
         __syncwarp();
         const uint32_t nc = c + kStreamStages;
         if (lane == 0 && nc < n_chunks) {
             const uint32_t ncnt = min((uint32_t)kStreamChunk, n_pad - nc * kStreamChunk);
-            stream_issue(ws.stage + st * kStreamChunk, slab + nc * kF4, ncnt * 12u, ws.bar + st);
+            stream_issue(ws.stage + st * kF4, slab + nc * kF4, ncnt * 12u, ws.bar + st);
         }
         if (((c + 1) * kStreamChunk) % kPairsMaxSpheres == 0 || c + 1 == n_chunks) {
             refine_queue(fetch_scan, queue, qn, rays);
@@ -360,8 +360,8 @@ render_pool(const __grid_constant__ KernelParams P) {
     WarpStream ws;
     {
         unsigned char *base = reinterpret_cast<unsigned char *>(ctl) + ((sizeof(PoolCtl) + 15u) & ~15u);
-        ws.stage = reinterpret_cast<float4 *>(base) + (tid >> 5) * (kStreamStages * kStreamChunk);
-        ws.bar = reinterpret_cast<uint64_t *>(base + (size_t)(THREADS / 32) * kStreamStages * kStreamChunk * sizeof(float4)) + (tid >> 5) * kStreamStages;
+        ws.stage = reinterpret_cast<float4 *>(base) + (tid >> 5) * (kStreamStages * kStreamStageF4);
+        ws.bar = reinterpret_cast<uint64_t *>(base + (size_t)(THREADS / 32) * kStreamStages * kStreamStageF4 * sizeof(float4)) + (tid >> 5) * kStreamStages;
         ws.parity = 0u;
     }
 #define SRT_ST(f, id) st[(f) * NS + (id)]
@@ -769,6 +769,8 @@ static render_kernel_t pick_pool_kernel_cfg(const srt_scene_options &o) {
     return o.fma_dot ? render_pool<8, true, THREADS, MINB, STREAM> : render_pool<8, false, THREADS, MINB, STREAM>;
 }
 static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream, int threads) {
+    if (stream && threads == 768 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 768, 1, true>;   // experiment
+    if (stream && threads == 512 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 512, 1, true>;   // experiment
     if (stream) return pick_pool_kernel_cfg<kPoolThreads, kPoolMinBlocks, true>(o);
     if (threads == 896) return pick_pool_kernel_cfg<896, 1, false>(o);
     if (threads == 512) return pick_pool_kernel_cfg<512, 1, false>(o);
@@ -777,7 +779,7 @@ static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream,
 static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
     const size_t ns = 64u * (threads / 32 + kPoolSpareBatches), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
     size_t bytes = (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
-    if (stream) bytes += warps * kStreamStages * (kStreamChunk * sizeof(float4) + sizeof(uint64_t));
+    if (stream) bytes += warps * kStreamStages * (kStreamStageF4 * sizeof(float4) + sizeof(uint64_t));
     else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
     return bytes;
 }
@@ -1102,13 +1104,16 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         if (P.done_tag == 0u && n_chunks > 1u)   // sequence wrapped: forget counts of 2^20 launches ago
             SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
     }
-    if (stream || !pool_res_fit) pool_threads = kPoolThreads;
+    if (stream || !pool_res_fit) {
+        pool_threads = kPoolThreads;
+        if (const char *v = getenv("SRT_STREAM_THREADS")) { const int t = atoi(v); if ((t == 512 || t == 768) && b->opt.lane_width == 8 && b->opt.fma_dot) pool_threads = t; }
+    }
     render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
     const int threads = pool ? pool_threads : pairs ? pc.threads : kBlockThreads;
     const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (pool) {   // leave the rest of the 256 KB to L1: the candidate queues live in local memory
-        const size_t ctas = stream ? kPoolMinBlocks : 1;
+        const size_t ctas = pool_threads == kPoolThreads && stream ? kPoolMinBlocks : 1;
         const int carve = (int)std::min<size_t>(100, (ctas * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
         SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     }

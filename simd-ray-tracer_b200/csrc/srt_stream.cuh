@@ -14,8 +14,15 @@
 
 namespace srt {
 
-constexpr int kStreamChunk = 64;     // spheres per stage (1 KiB)
-constexpr int kStreamStages = 4;     // stages per warp (4 KiB per warp)
+#ifndef SRT_STREAM_CHUNK
+#define SRT_STREAM_CHUNK 256
+#endif
+#ifndef SRT_STREAM_STAGES
+#define SRT_STREAM_STAGES 2
+#endif
+constexpr int kStreamChunk = SRT_STREAM_CHUNK;        // spheres per stage
+constexpr int kStreamStageF4 = kStreamChunk * 3 / 4;  // float4 per stage: the slab table has 12 B per sphere
+constexpr int kStreamStages = SRT_STREAM_STAGES;      // stages per warp
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -37,7 +44,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
 
 // Per-warp stream state: the ring of stages and the parity each stage's barrier will show next.
 struct WarpStream {
-    float4 *stage;          // kStreamStages x kStreamChunk float4, this warp's
+    float4 *stage;          // kStreamStages x kStreamStageF4 float4, this warp's
     uint64_t *bar;          // kStreamStages barriers, this warp's
     uint32_t parity;        // bit s = parity to wait for on stage s
 };
