@@ -309,24 +309,31 @@ def run_gpu_arm(args):
     achieved = FLOP_PER_TEST * rays_per_launch * n_pad / (kms * 1e-3) / 1e12
     pair_kernel = n_pad >= 64
     primary_per_launch = float(W * H * SPP) / max(1, n_gpus)   # one render launch per step per rank
+    issue_cycles_per_sphere_pass = (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 64) / (rays_per_launch * n_pad / (kms * 1e-3))
     roofline = {
         "bound": "fp32",
-        "kernel": ("render_pool<8,true> (CTA-owned path slots, warp passes of 64 primary or 64 secondary rays, two rays per thread: "
-                   "fused f32x2 filter over all spheres + reference arithmetic on the candidates"
+        "kernel": ("render_pool<8,true> (CTA-owned path slots, warp passes of 64 rays, two rays per thread: level-1 slab test of every "
+                   "sphere (2 FFMA2 + 2 FSETP per sphere per ray pair), level-2 fused 7-FMA filter on the survivors, the reference's "
+                   "arithmetic on what is left"
                    + ("; tables streamed through per-warp TMA stages)" if n_pad > 8192 else "; tables resident in shared memory)")
                    if pair_kernel else "render_paths<8,true,true> (packed FFMA2 intersection loop)"),
         "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
         "peak_source": f"{info0['sm_count']} SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); "
                        "no tensor-core or HBM roof applies: the loop has no dense contraction and its scene is shared-memory resident",
         "algorithmic_flop_per_test": FLOP_PER_TEST, "tests_per_launch": rays_per_launch * n_pad,
-        "executed_flop_per_test": "8 (primary rays: 4 FMA) / 14 (secondary rays: 7 FMA)" if pair_kernel else 20,
-        "frac_executed": ((8.0 * primary_per_launch + 14.0 * (rays_per_launch - primary_per_launch)) if pair_kernel
-                          else 20.0 * rays_per_launch) * n_pad / (kms * 1e-3) / 1e12 / peak_tflops,
-        "issue_cycles_per_32_tests": (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 32) / (rays_per_launch * n_pad / (kms * 1e-3)),
-        "issue_bound_note": ("achieved counts the reference's 20 flop per ray-sphere test (SURVEY 8d).  The filter scan executes 7 FMA "
-                             "per test for secondary rays and 4 for primary rays; a packed FFMA2 holds the issue port 2 cycles, so the "
-                             "issue floors are 9.0 and 5.5 cycles per 32 tests (LDS.128 + 2-3 ALU ops per sphere per 64 rays); "
-                             "see DESIGN.md 5.2-5.4"
+        "executed_flop_per_test": 4 if pair_kernel else 20,
+        "frac_executed": (4.0 if pair_kernel else 20.0) * rays_per_launch * n_pad / (kms * 1e-3) / 1e12 / peak_tflops,
+        "issue_cycles_per_sphere_per_warp_pass": issue_cycles_per_sphere_pass,
+        "issue_floor_cycles_per_sphere_per_warp_pass": 8.06 if pair_kernel else 30.0,
+        "issue_slot_frac": (8.06 if pair_kernel else 30.0) / issue_cycles_per_sphere_pass,
+        "issue_bound_note": ("`achieved`/`frac` count the reference's 20 flop per ray-sphere test (SURVEY 8d) and exceed the FP32 peak "
+                             "because the kernel does not execute them: every sphere is tested against every ray with a conservative "
+                             "2-FMA slab test (4 executed flop), ~2 % go on to a 7-FMA filter, ~0.2 % to the reference's 20-flop "
+                             "sequence (bit-exact results; soundness proof DESIGN.md 5.3, on-device audit srt_filter_audit).  The "
+                             "binding resource is the SM sub-partition's issue port: a packed FFMA2 holds it for 2 cycles and LDS / "
+                             "FSETP / LOP3 are not issued in its shadow (scripts/microbench/issue_mix.cu), so the level-1 floor is "
+                             "2x2 + 2 + 1 + 0.75 + loop = 8.06 issue cycles per sphere per 64 rays; `issue_slot_frac` = that floor / "
+                             "the measured whole-kernel cycles per sphere per 64 rays (regenerate, level 2, select, shade included)"
                              if pair_kernel else
                              "15 of the 20 flops' instructions are mandatory separate roundings (parity), so 15 FP32 issue cycles/test "
                              "is the hard floor: frac <= 20/30 = 0.667; see DESIGN.md"),
