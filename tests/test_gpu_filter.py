@@ -266,3 +266,58 @@ def test_pool_sample_chunks_fold_in_order(srt, oracle, monkeypatch, chunk):
             assert np.array_equal(b.read_accum()[..., :3].view(np.uint32), o_acc[..., :3].view(np.uint32))
     finally:
         b.close()
+
+
+@pytest.mark.parametrize("axis", ["0", "1", "2"])
+def test_slab_axis_never_changes_results(srt, oracle, monkeypatch, axis):
+    """Level 1 (slab test): the slab axis affects selectivity only.  Every axis gives the oracle's
+    bits on a resident and on a streamed (variant 12) run, and a clean audit."""
+    monkeypatch.setenv("SRT_SLAB_AXIS", axis)
+    spheres, sky, hdr = srt.host_scene(2)
+    w, h = 96, 54
+    cam = srt.host_camera(2, w, h, hdr)
+    o = oracle.render(spheres, sky, 8, 1, cam, w, h, 0, 2)
+    for variant in ("0", "12"):
+        monkeypatch.setenv("SRT_KERNEL_VARIANT", variant)
+        b = srt.Backend(0)
+        try:
+            assert _same(o, _render(b, spheres, sky, 8, 1, cam, w, h, 2)) == {}, (axis, variant)
+            a = b.filter_audit(cam, 0, 1)
+            assert a["violations"] == 0 and a["slab_survivors"] >= a["candidates"] >= a["hits"], a
+        finally:
+            b.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_slab_degenerate_rays_and_far_camera(backend, srt, oracle, mode):
+    """Rays parallel to the slab axis (U undefined -> every sphere is a candidate), a column of
+    spheres along that axis, axis-aligned view directions, and a camera far outside the scene's
+    origin bound (the slab radii are inflated for the camera distance)."""
+    W, fma = mode
+    diff = ((0.7, 0.3, 0.3), (0, 0, 0), 0.0, 0.0)
+    glass = ((1, 1, 1), (0, 0, 0), 0.0, 1.5)
+    lamp = ((0.9, 0.9, 0.9), (2, 2, 2), 0.0, 0.0)
+    # a column along y (centres spread along y only -> the slab axis is x or z), mirrors and glass in it
+    rows = [(0.0, -1000.5, 0.0, 1000.0, (0.5, 0.5, 0.5), (0, 0, 0), 0.0, 0.0)]
+    rows += [(0.0, 0.6 * i, 0.0, 0.25, *(glass if i % 3 == 0 else (lamp if i % 3 == 1 else diff))) for i in range(70)]
+    sp = _mk(srt, rows)
+    w, h = 64, 48
+    views = []
+    for pos, z in (((0.0, 60.0, 0.0), (0, 1, 0)),         # straight down the column: primary rays ~ parallel to y
+                   ((6.0, 20.0, 0.0), (1, 0, 0)),          # along -x
+                   ((0.0, 20.0, 6.0), (0, 0, 1)),          # along -z
+                   ((0.0, 20.0, 9000.0), (0, 0, 1))):      # far camera: |O| >> scene bound
+        cam = np.zeros(1, srt.camera_dtype)
+        zz = np.array(z, np.float32)
+        xx = np.array((1, 0, 0) if z[0] == 0 else (0, 0, -1), np.float32)
+        yy = np.cross(zz, xx).astype(np.float32)
+        cam["position"][0, :3] = pos; cam["z"][0, :3] = zz; cam["x"][0, :3] = xx; cam["y"][0, :3] = yy
+        cam["film_center"][0, :3] = np.array(pos, np.float32) - zz
+        cam["film_w"][0] = 1.0; cam["film_h"][0] = h / w
+        views.append(cam)
+    for cam in views:
+        o = oracle.render(sp, True, W, fma, cam, w, h, 0, 2)
+        g = _render(backend, sp, True, W, fma, cam, w, h, 2)
+        assert _same(o, g) == {}
+        a = backend.filter_audit(cam, 0, 1)
+        assert a["violations"] == 0, a
