@@ -27,16 +27,31 @@ static bool WritePpm(const char *Path, const u32 *Pixels, u32 W, u32 H) {
     return true;
 }
 
+// PFM (portable float map): RGB f32, little endian, rows bottom-up -- the accumulator's own row order.
+static bool WritePfm(const char *Path, const f32 *Accum, u32 W, u32 H) {
+    FILE *F = fopen(Path, "wb");
+    if (!F) return false;
+    fprintf(F, "PF\n%u %u\n-1.0\n", W, H);
+    std::vector<f32> Row((size_t)W * 3);
+    for (u32 y = 0; y < H; ++y) {
+        const f32 *Src = Accum + (size_t)y * W * 4;
+        for (u32 x = 0; x < W; ++x) { Row[x * 3 + 0] = Src[x * 4 + 0]; Row[x * 3 + 1] = Src[x * 4 + 1]; Row[x * 3 + 2] = Src[x * 4 + 2]; }
+        fwrite(Row.data(), sizeof(f32), Row.size(), F);
+    }
+    return fclose(F) == 0;
+}
+
 static void Usage() {
     fprintf(stderr,
             "usage: srt_headless [--scene 0..4] [--width W] [--height H] [--spp N] [--spf K]\n"
             "                    [--simd 0|1] [--lanes 4|8] [--fma 0|1] [--device D] [--stream-base B]\n"
             "                    [--orbit FRAMES] [--out image.ppm] [--accum accum.f32]\n"
             "                    [--scene-file in.scene] [--dump-scene out.scene]\n"
-            "                    [--checkpoint out.ckpt] [--resume in.ckpt]\n"
+            "                    [--checkpoint out.ckpt] [--resume in.ckpt] [--pfm accum.pfm] [--threads N]\n"
             "  scenes: 0 RGB Glass, 1 Floating Spheres, 2 One Weekend, 3 synthetic 1,024, 4 synthetic 65,536\n"
             "  --scene-file replaces slot --scene by the file's scene; --dump-scene writes slot --scene as text.\n"
             "  --resume continues a checkpoint (same size, scene, stream base): --spp more samples are added.\n"
+            "  --pfm writes the linear accumulator as a PFM image.  --threads is render_params.ThreadCount: accepted, ignored on the GPU.\n"
             "  --spf: samples per OnRender frame (reference: 1).  --orbit: hold key A for FRAMES frames first.\n");
 }
 
@@ -44,7 +59,8 @@ int main(int argc, char **argv) {
     u32 Scene = 0, W = 1280, H = 720, Spp = 1, Spf = 1, Orbit = 0;
     bool Simd = true;
     backend_params BP;
-    const char *Out = nullptr, *AccumOut = nullptr, *SceneFile = nullptr, *DumpScene = nullptr, *CkptOut = nullptr, *CkptIn = nullptr;
+    const char *Out = nullptr, *AccumOut = nullptr, *SceneFile = nullptr, *DumpScene = nullptr, *CkptOut = nullptr, *CkptIn = nullptr, *PfmOut = nullptr;
+    u32 ThreadCount = 0;
     for (int i = 1; i < argc; ++i) {
         std::string A = argv[i];
         auto Next = [&]() -> const char * { if (i + 1 >= argc) { Usage(); exit(2); } return argv[++i]; };
@@ -65,6 +81,8 @@ int main(int argc, char **argv) {
         else if (A == "--dump-scene") DumpScene = Next();
         else if (A == "--checkpoint") CkptOut = Next();
         else if (A == "--resume") CkptIn = Next();
+        else if (A == "--pfm") PfmOut = Next();
+        else if (A == "--threads") ThreadCount = atoi(Next());
         else { Usage(); return 2; }
     }
     if (Spf == 0) Spf = 1;
@@ -102,7 +120,7 @@ int main(int argc, char **argv) {
 
     std::vector<u32> Present((size_t)W * H);
     image Image = { Present.data(), W, H, format::R8G8B8A8_U32 };
-    render_params RP = { 0, Simd, Scene };
+    render_params RP = { ThreadCount, Simd, Scene };
 
     // Optional scripted orbit: hold A so every frame resets, like a user dragging the camera.
     u64 Rays = 0, TotalRays = 0;
@@ -142,6 +160,11 @@ int main(int argc, char **argv) {
         ReadAccumulator(Acc.data());
         checkpoint_header Hd = { W, H, GetAccumulatedSampleCount(), Scene, BP.StreamBase, Simd ? BP.LaneWidth : 1u, (u32)(Simd && BP.FmaDot) };
         if (!SaveCheckpoint(CkptOut, Hd, Acc.data())) { fprintf(stderr, "cannot write %s\n", CkptOut); return 1; }
+    }
+    if (PfmOut) {
+        std::vector<f32> Acc((size_t)W * H * 4);
+        ReadAccumulator(Acc.data());
+        if (!WritePfm(PfmOut, Acc.data(), W, H)) { fprintf(stderr, "cannot write %s\n", PfmOut); return 1; }
     }
     if (AccumOut) {
         std::vector<f32> Acc((size_t)W * H * 4);

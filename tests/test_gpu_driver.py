@@ -92,3 +92,17 @@ def test_driver_checkpoint_resume_and_scene_file(srt, oracle, tmp_path):
     s_a, a_a, _ = run_driver(srt, tmp_path, "--scene", 2, "--width", w, "--height", h, "--spp", 2)
     s_b, a_b, _ = run_driver(srt, tmp_path, "--scene", 0, "--scene-file", sf, "--width", w, "--height", h, "--spp", 2)
     assert np.array_equal(a_a.view(np.uint32), a_b.view(np.uint32)) and s_a["rays"] == s_b["rays"] and s_b["spheres"] == s_a["spheres"]
+
+
+def test_driver_pfm_and_thread_count(srt, tmp_path):
+    """N2/N3: the PFM dump is the accumulator (RGB, bottom-up rows); --threads is accepted and changes nothing."""
+    w, h = 48, 27
+    pfm = tmp_path / "a.pfm"
+    s1, a1, _ = run_driver(srt, tmp_path, "--scene", 1, "--width", w, "--height", h, "--spp", 2, "--pfm", pfm, "--threads", 7)
+    s2, a2, _ = run_driver(srt, tmp_path, "--scene", 1, "--width", w, "--height", h, "--spp", 2)
+    assert np.array_equal(a1.view(np.uint32), a2.view(np.uint32)) and s1["rays"] == s2["rays"]
+    raw = pfm.read_bytes()
+    head = f"PF\n{w} {h}\n-1.0\n".encode()
+    assert raw.startswith(head) and len(raw) == len(head) + w * h * 12
+    rgb = np.frombuffer(raw[len(head):], np.float32).reshape(h, w, 3)
+    assert np.array_equal(rgb.view(np.uint32), a1.reshape(h, w, 4)[..., :3].view(np.uint32))

@@ -321,3 +321,48 @@ def test_slab_degenerate_rays_and_far_camera(backend, srt, oracle, mode):
         assert _same(o, g) == {}
         a = backend.filter_audit(cam, 0, 1)
         assert a["violations"] == 0, a
+
+
+def test_full_size_4k_properties(srt, monkeypatch):
+    """BASELINE configs[2] at its full image size (3840x2160, 1,024 spheres), too large for the CPU
+    oracle: size-independent properties instead.  (1) the production kernel equals the kernel that
+    runs the reference's arithmetic on every sphere, bit for bit, on all 8.3 M pixels; (2) two
+    launches of 2 spp equal one launch of 4 spp; (3) a resumed accumulator (srt_write_accum) continues
+    identically; (4) 4 strided SUM shards resolve to within 1 LSB / 60 dB of the exact running mean."""
+    w, h, spp = 3840, 2160, 4
+    spheres, sky, hdr = srt.host_scene(3)
+    cam = srt.host_camera(3, w, h, hdr)
+    b = srt.Backend(0)
+    try:
+        monkeypatch.setenv("SRT_KERNEL_VARIANT", "7")
+        ref = _render(b, spheres, sky, 8, 1, cam, w, h, spp)
+        monkeypatch.delenv("SRT_KERNEL_VARIANT")
+        auto = _render(b, spheres, sky, 8, 1, cam, w, h, spp)
+        assert _same(ref, auto) == {}
+        assert ref["rays"] > w * h * spp
+        b.reset()
+        b.render(cam, 0, 2); r1 = b.wait()[1]
+        half = b.read_accum()
+        b.render(cam, 2, 2); r2 = b.wait()[1]
+        assert np.array_equal(b.read_accum().view(np.uint32), ref["accum"].view(np.uint32)) and r1 + r2 == ref["rays"]
+        b.reset()
+        b.write_accum(half)
+        b.render(cam, 2, 2); b.wait()
+        assert np.array_equal(b.read_accum().view(np.uint32), ref["accum"].view(np.uint32))
+        assert np.array_equal(b.read_rgba8(), ref["rgba"])
+        b.reset()
+        rays = 0
+        for shard in range(4):
+            b.render(cam, shard, 1, stride=4, mode=1)
+            rays += b.wait()[1]
+        b.resolve_sum(spp)
+        assert rays == ref["rays"]
+        acc = b.read_accum()[..., :3].astype(np.float64)
+        want = ref["accum"][..., :3].astype(np.float64)
+        mse = float(np.mean((acc - want) ** 2))
+        peak = float(max(want.max(), 1.0))
+        assert 10 * np.log10(peak * peak / max(mse, 1e-30)) >= 60.0
+        d = np.abs(b.read_rgba8().view(np.uint8).astype(np.int16) - ref["rgba"].view(np.uint8).astype(np.int16)).max()
+        assert d <= 1, d
+    finally:
+        b.close()
