@@ -233,20 +233,26 @@ def run_gpu_arm(args):
     if rank == 0:
         sampler.start()
     kernel_ms.clear(); kernel_rays.clear()
+    # Device-side clock: CUDA events on the stream every launch of a step goes to (the backend's
+    # own stream, which also carries the memset and the NCCL reduce); wall clock kept beside it.
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
+    ev0.record(ext_stream)
     rays_local = 0
     for _ in range(args.steps):
         rays_local += step()
+    ev1.record(ext_stream)
     barrier()
-    elapsed = time.perf_counter() - t0
+    wall_elapsed = time.perf_counter() - t0
+    elapsed = ev0.elapsed_time(ev1) * 1e-3
     clocks = sampler.stop() if rank == 0 else None
     launches = b.device_info()["launches"] - launches0
 
-    t = torch.tensor([elapsed, float(rays_local), float(launches), float(np.mean(kernel_ms))], dtype=torch.float64, device="cuda")
+    t = torch.tensor([elapsed, float(rays_local), float(launches), float(np.mean(kernel_ms)), wall_elapsed], dtype=torch.float64, device="cuda")
     if dist is not None:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
-        elapsed, rays_total, launches_total, kms = tmax[0].item(), tsum[1].item(), tsum[2].item(), tmax[3].item()
+        elapsed, rays_total, launches_total, kms, wall_elapsed = tmax[0].item(), tsum[1].item(), tsum[2].item(), tmax[3].item(), tmax[4].item()
     else:
         elapsed, rays_total, launches_total, kms = t[0].item(), t[1].item(), t[2].item(), t[3].item()
     value = rays_total / elapsed / 1e6
@@ -348,6 +354,29 @@ def run_gpu_arm(args):
         except (OSError, ValueError):
             pass
 
+    # ---- HBM roofline of accumulate/tonemap standalone (A8-A9): resolve_sum_kernel -------------
+    # 36 algorithmic bytes per pixel (16 R + 16 W accumulator, 4 W RGBA8); at N = 1 the
+    # path kernel does this work itself, so the kernel is timed here on the step's own buffers.
+    hbm = None
+    if not args.no_resolve_bench:
+        reps = 20
+        for _ in range(3):
+            b.resolve_sum(SPP)
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record(ext_stream)
+        for _ in range(reps):
+            b.resolve_sum(SPP)
+        r1.record(ext_stream)
+        b.wait()
+        torch.cuda.synchronize()
+        r_ms = r0.elapsed_time(r1) / reps
+        gbs = 36.0 * W * H / (r_ms * 1e-3) / 1e9
+        peak_gbs = float(peaks.get("hbm_gbs", 6451.8))
+        hbm = {"bound": "hbm", "kernel": "resolve_sum_kernel (mean + tonemap + pack after the cross-GPU sum)", "achieved": gbs, "peak": peak_gbs,
+               "unit": "GB/s", "frac": gbs / peak_gbs, "bytes_per_pixel": 36, "pixels": W * H, "launch_us": r_ms * 1e3, "launches": reps,
+               "l2": f"working set {20 * W * H / 1e6:.0f} MB " + ("> 126 MB L2" if 20 * W * H > 126e6 else "fits the 126 MB L2: not an HBM number"),
+               "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth, burst)", "traffic": None}
+
     # ---- secondary metric: ms/frame @1080p, progressive 1 spp/frame (BASELINE configs[3]) --------
     lat = None
     if n_gpus == 1 and not args.no_latency:
@@ -357,15 +386,15 @@ def run_gpu_arm(args):
         b.set_scene(s0, sky0, LANE_WIDTH, FMA_DOT)
         b.resize(1920, 1080)
         dev, wall = [], []
-        for k in range(args.latency_frames + 20):
+        for k in range(args.latency_frames + 50):
             tw = time.perf_counter()
             b.render(cam0, k, 1)
             ms, _ = b.wait()
-            if k >= 20:
+            if k >= 50:
                 dev.append(ms); wall.append((time.perf_counter() - tw) * 1e3)
         lat = {"frames": len(dev), "device_ms_p50": float(np.percentile(dev, 50)), "device_ms_p99": float(np.percentile(dev, 99)),
                "wall_ms_p50": float(np.percentile(wall, 50)), "wall_ms_p99": float(np.percentile(wall, 99)),
-               "protocol": "scene 0, 1920x1080, 1 spp/frame, exact running mean on device, read-back excluded"}
+               "protocol": "BASELINE configs[3]: scene 0, 1920x1080, 1 spp/frame, 50 warm-up frames, exact running mean on device, read-back excluded"}
 
     # ---- CPU baseline: the reference's own code on this box's host cores, bounded sample ---------
     cpu = None
@@ -380,6 +409,8 @@ def run_gpu_arm(args):
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
+        "timing": "CUDA events on the launching stream around the K steps, max over ranks; wall clock of the same region in wall_ms_per_step",
+        "wall_ms_per_step": wall_elapsed * 1e3 / args.steps,
         "config": {"workload": args.workload, "description": desc, "spheres": int(len(spheres)), "width": W, "height": H, "spp": SPP,
                    "max_bounces": 5, "lane_width": LANE_WIDTH, "fma_dot": FMA_DOT,
                    "parallelism": f"sample-sharded x{n_gpus}" + (" + NCCL reduce(sum) to rank 0" if n_gpus > 1 else " (exact running mean)"),
@@ -394,6 +425,8 @@ def run_gpu_arm(args):
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if hbm is not None:
+        line["roofline_hbm"] = hbm
     if lat is not None:
         line["frame_latency_1080p"] = lat
     print(json.dumps(line), file=_STDOUT, flush=True)
@@ -413,9 +446,10 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="synth1k_4k_256spp", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="wall-time budget of the CPU baseline sample")
-    ap.add_argument("--latency-frames", type=int, default=300)
+    ap.add_argument("--latency-frames", type=int, default=1000)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
+    ap.add_argument("--no-resolve-bench", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version
     # banner there) are sent to stderr while the benchmark runs.

@@ -654,7 +654,26 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
 }
 
 // mean = sum * (1/N); tonemap + pack.  HBM-bound: 16 B read + 16 B + 4 B written per pixel.
-__global__ void resolve_sum_kernel(float4 *accum, uint32_t *rgba, uint32_t n_pixels, float inv_n) {
+// Two adjacent pixels per thread: both 16-byte loads are issued before anything depends on them
+// (a warp reads 1 KiB contiguous), the two RGBA8 words go out as one 8-byte store.
+__global__ void __launch_bounds__(256) resolve_sum_kernel(float4 *__restrict__ accum, uint32_t *__restrict__ rgba, uint32_t n_pixels, float inv_n) {
+    const uint32_t i = 2u * (blockIdx.x * blockDim.x + threadIdx.x);
+    if (i + 1u < n_pixels) {
+        const float4 s0 = __ldcs(accum + i), s1 = __ldcs(accum + i + 1u);
+        const float r0 = __fmul_rn(s0.x, inv_n), g0 = __fmul_rn(s0.y, inv_n), b0 = __fmul_rn(s0.z, inv_n);
+        const float r1 = __fmul_rn(s1.x, inv_n), g1 = __fmul_rn(s1.y, inv_n), b1 = __fmul_rn(s1.z, inv_n);
+        accum[i] = make_float4(r0, g0, b0, 1.0f);
+        accum[i + 1u] = make_float4(r1, g1, b1, 1.0f);
+        *reinterpret_cast<uint2 *>(rgba + i) = make_uint2(pack_rgba8(r0, g0, b0), pack_rgba8(r1, g1, b1));
+    } else if (i < n_pixels) {
+        const float4 s = accum[i];
+        const float r = __fmul_rn(s.x, inv_n), g = __fmul_rn(s.y, inv_n), b = __fmul_rn(s.z, inv_n);
+        accum[i] = make_float4(r, g, b, 1.0f);
+        rgba[i] = pack_rgba8(r, g, b);
+    }
+}
+// one pixel per thread (SRT_RESOLVE_VARIANT=1; kept for A/B measurements)
+__global__ void __launch_bounds__(256) resolve_sum_kernel_1px(float4 *accum, uint32_t *rgba, uint32_t n_pixels, float inv_n) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_pixels) return;
     const float4 s = accum[i];
@@ -1210,7 +1229,12 @@ int srt_resolve_sum(srt_backend *b, uint32_t total_samples) {
     const uint32_t n = b->width * b->height;
     const volatile float one = 1.0f;
     const float inv_n = one / (float)total_samples;
-    resolve_sum_kernel<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->d_rgba, n, inv_n);
+    static const int variant = getenv("SRT_RESOLVE_VARIANT") ? atoi(getenv("SRT_RESOLVE_VARIANT")) : 0;
+    // the 8-byte RGBA8 store of the two-pixel kernel needs an 8-byte aligned image (cudaMalloc / torch buffers are)
+    if (variant == 1 || (reinterpret_cast<uintptr_t>(b->d_rgba) & 7u) != 0)
+        resolve_sum_kernel_1px<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->d_rgba, n, inv_n);
+    else
+        resolve_sum_kernel<<<((n + 1) / 2 + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->d_rgba, n, inv_n);
     SRT_CUDA(b, cudaGetLastError());
     b->launches += 1;
     b->in_flight = true;
