@@ -118,10 +118,12 @@ int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays);
  * (csrc/srt_pairs.cuh: level 1 slab test, level 2 fused 7-FMA test).  Traces the same paths as srt_render(first_sample, n_samples) would,
  * with the reference's per-lane arithmetic, and for EVERY (path segment, sphere) pair evaluates
  * both the reference's hit predicate (main.cpp:409 / :557) and the filter predicate.  Blocking.
- * out_counts = { tests, exact hits, candidates (pass both levels), violations, level-1 survivors };
- * the filters are sound iff violations (an exact hit either level would have dropped) is 0.
+ * out_counts = { tests, exact hits, candidates (pass both levels), violations, level-1 survivors,
+ *                primary-ray tests of bundled pixels, level-0 (pixel bundle, csrc/srt_bundle.cuh) candidates,
+ *                level-0 violations };
+ * the filters are sound iff both violation counts (an exact hit a level would have dropped) are 0.
  * Touches no image buffer. */
-int srt_filter_audit(srt_backend *b, const srt_camera *camera, const srt_render_args *args, uint64_t out_counts[5]);
+int srt_filter_audit(srt_backend *b, const srt_camera *camera, const srt_render_args *args, uint64_t out_counts[8]);
 
 /* accum holds a SUM over `total_samples`: mean = sum * (1/N), tonemap + pack into rgba
  * (main.cpp:312-346). Asynchronous on the backend stream; ordered after prior renders. */

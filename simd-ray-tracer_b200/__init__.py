@@ -149,12 +149,14 @@ class Backend:
         return ms.value, rays.value
 
     def filter_audit(self, camera, first_sample=0, n_samples=1, stream_base=0):
-        """Soundness audit of the sphere filters: dict(tests, hits, candidates, violations, slab_survivors)."""
+        """Soundness audit of the sphere filters: dict(tests, hits, candidates, violations, slab_survivors,
+        bundle_tests, bundle_candidates, bundle_violations)."""
         cam = np.ascontiguousarray(camera)
         args = RenderArgs(first_sample, n_samples, 1, ACCUM_MEAN, stream_base, 0, 0)
-        counts = (C.c_uint64 * 5)()
+        counts = (C.c_uint64 * 8)()
         self._check(self.L.srt_filter_audit(self.h, cam.ctypes.data, C.byref(args), counts))
-        return dict(tests=counts[0], hits=counts[1], candidates=counts[2], violations=counts[3], slab_survivors=counts[4])
+        return dict(tests=counts[0], hits=counts[1], candidates=counts[2], violations=counts[3], slab_survivors=counts[4],
+                    bundle_tests=counts[5], bundle_candidates=counts[6], bundle_violations=counts[7])
 
     def resolve_sum(self, total_samples):
         self._check(self.L.srt_resolve_sum(self.h, total_samples))

@@ -10,9 +10,11 @@
 #include "srt_pairs.cuh"
 #include "srt_path.cuh"
 #include "srt_pool.cuh"
+#include "srt_bundle.cuh"
 #include "srt_stream.cuh"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -340,7 +342,78 @@ __device__ __forceinline__ void stream_pass(WarpStream &ws, const float4 *__rest
     }
 }
 
-template <int W, bool FMA, int THREADS, int MINB, bool STREAM>
+// Bundle mode, streamed scenes: the level-0 scan reads the launch's slab table straight from global memory
+// (L2; every lane a different 48-byte group, coalesced), refine + select per kPairsMaxSpheres segment.
+template <int W, bool FMA>
+__device__ __forceinline__ void stream_bundle_pass(const float4 *__restrict__ slab, const float4 *__restrict__ scan, const float4 *__restrict__ spheres,
+                                                   uint32_t n_pad, uint32_t n_real, float op, float oq, unsigned heads0, unsigned heads1,
+                                                   const BundlePixel &bp0, const BundlePixel &bp1, const ScanRays &rays, unsigned lane,
+                                                   pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, float neg_one, float one, Best &b0, Best &b1) {
+    CandQueue queue;
+    const FetchGlobal fetch = {spheres};
+    const FetchScanGlobal fetch_scan = {scan};
+#pragma unroll 1
+    for (uint32_t first = 0; first < n_pad; first += (uint32_t)kPairsMaxSpheres) {
+        uint32_t qn = 0;
+        bundle_scan<true>(slab, first, min((uint32_t)kPairsMaxSpheres, n_pad - first), op, oq, heads0, heads1, bp0, bp1, lane, queue, qn);
+        refine_queue(fetch_scan, queue, qn, rays);
+        select_update<W, FMA>(fetch, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one, one, b0, b1);
+    }
+}
+
+// Bundle mode, A8 (+ A9): all samples of chunk c of pixel `pix` are staged in row `row`; fold them into the
+// running mean in sample order (main.cpp:484-489 is sequential in k), publish the chunk count.  Called by
+// the whole warp with uniform arguments: lane l fetches samples l and l + 32 and their weights in parallel,
+// the recurrence itself is serial.
+__device__ __noinline__ void fold_bundle(const KernelParams &P, uint32_t pix, uint32_t row, uint32_t c, unsigned lane) {
+    __threadfence();                                                      // the other samples' staging stores
+    const uint32_t S = 1u << P.bundle_log2, n0 = c << P.bundle_log2;
+    const uint32_t nvalid = min(S, P.n_samples - n0);
+    const float4 *st = P.stage + ((size_t)row << P.bundle_log2);
+    float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
+    float wb0 = 0.0f, wb1 = 0.0f;
+    if (lane < nvalid) v0 = __ldcg(st + lane);
+    if (lane + 32u < nvalid) v1 = __ldcg(st + lane + 32u);
+    const bool mean_mode = P.accum_mode == SRT_ACCUM_MEAN;
+    if (mean_mode) {                                                      // Out * (1/N), PrevCount/N with N = k + 1 (host table, IEEE)
+        const float2 w0 = lane < nvalid ? __ldg(P.fold_w + n0 + lane) : make_float2(0.f, 0.f);
+        const float2 w1 = lane + 32u < nvalid ? __ldg(P.fold_w + n0 + lane + 32u) : make_float2(0.f, 0.f);
+        wb0 = w0.y; wb1 = w1.y;
+        v0.x = __fmul_rn(w0.x, v0.x); v0.y = __fmul_rn(w0.x, v0.y); v0.z = __fmul_rn(w0.x, v0.z);
+        v1.x = __fmul_rn(w1.x, v1.x); v1.y = __fmul_rn(w1.x, v1.y); v1.z = __fmul_rn(w1.x, v1.z);
+    }
+    float4 m = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                       // PreviousColor * (0/1), zeroed arena
+    if (c != 0u || P.first_sample > 0u || !mean_mode) m = __ldcg(&P.accum[pix]);
+#pragma unroll 1
+    for (uint32_t j = 0; j < nvalid; ++j) {
+        const bool hi = j >= 32u;
+        const float ux = __shfl_sync(0xFFFFFFFFu, hi ? v1.x : v0.x, j & 31u);
+        const float uy = __shfl_sync(0xFFFFFFFFu, hi ? v1.y : v0.y, j & 31u);
+        const float uz = __shfl_sync(0xFFFFFFFFu, hi ? v1.z : v0.z, j & 31u);
+        if (mean_mode) {
+            const float wb = __shfl_sync(0xFFFFFFFFu, hi ? wb1 : wb0, j & 31u);
+            m.x = __fadd_rn(ux, __fmul_rn(wb, m.x)); m.y = __fadd_rn(uy, __fmul_rn(wb, m.y)); m.z = __fadd_rn(uz, __fmul_rn(wb, m.z));
+        } else {
+            m.x = __fadd_rn(m.x, ux); m.y = __fadd_rn(m.y, uy); m.z = __fadd_rn(m.z, uz);
+        }
+    }
+    if (c + 1u == P.n_chunks && mean_mode) {                              // A9, one channel per lane (one copy of the sqrt)
+        const float v = lane == 0 ? m.x : (lane == 1 ? m.y : m.z);
+        uint32_t q = to_u8(linear_to_srgb(v)) << (8u * (lane & 3u));
+        q |= __shfl_down_sync(0xFFFFFFFFu, q, 1);
+        q |= __shfl_down_sync(0xFFFFFFFFu, q, 2);
+        if (lane == 0) P.rgba[pix] = (q & 0x00FFFFFFu) | (255u << 24);
+    }
+    if (lane == 0) {
+        P.accum[pix] = make_float4(m.x, m.y, m.z, 1.0f);
+        P.cnt[row] = 0u;
+        __threadfence();                                                  // accum, cnt before the chunk count
+        *(volatile uint32_t *)&P.done[pix] = P.done_tag | (c + 1u);
+    }
+    __syncwarp();
+}
+
+template <int W, bool FMA, int THREADS, int MINB, bool STREAM, bool BUNDLE = false>
 __global__ void __launch_bounds__(THREADS, MINB)
 render_pool(const __grid_constant__ KernelParams P) {
     constexpr uint32_t NS = 64u * (THREADS / 32 + kPoolSpareBatches);   // slots per CTA
@@ -418,7 +491,91 @@ render_pool(const __grid_constant__ KernelParams P) {
         uint32_t qn = 0;
         uint32_t pend = 0;               // bit r: slot of half r waits for the preceding sample chunk of its pixel
         bool any_real = true;
-        if (kind == 0) {
+        BundlePixel bp0 = {0.0f, 0.0f, 0.0f, -1.0f}, bp1 = bp0;
+        unsigned heads0 = 0u, heads1 = 0u;
+        bool use_bundle = false;
+        if (BUNDLE && kind == 0) {
+            // ---- bundle mode: 64 free slots take 64 consecutive work items = consecutive samples of one pixel --
+            bool need0 = id0 != kRingEmpty && !(SRT_SU(S_FLAGS, id0) & kFlagPending);
+            bool need1 = id1 != kRingEmpty && !(SRT_SU(S_FLAGS, id1) & kFlagPending);
+            unsigned m0 = __ballot_sync(0xFFFFFFFFu, need0), m1 = __ballot_sync(0xFFFFFFFFu, need1);
+            unsigned n_retired = 0;
+            while (m0 | m1) {
+                unsigned base = 0;
+                if (lane == 0) base = atomicAdd(P.work_counter, (unsigned)(__popc(m0) + __popc(m1)));
+                base = __shfl_sync(0xFFFFFFFFu, base, 0);
+                const unsigned lt = (1u << lane) - 1u;
+#pragma unroll 1
+                for (int r = 0; r < 2; ++r) {
+                    if (r ? need1 : need0) {
+                        const uint32_t s = r ? id1 : id0;
+                        const uint32_t item = base + (r ? (uint32_t)(__popc(m0) + __popc(m1 & lt)) : (uint32_t)__popc(m0 & lt));
+                        bool need = true;
+                        if (item >= P.total_items) {                     // out of work: the slot retires
+                            SRT_SU(S_PIX, s) = kInvalidPixel;
+                            if (r) id1 = kRingEmpty; else id0 = kRingEmpty;
+                            n_retired += 1u;
+                            need = false;
+                        } else {
+                            BundleItem it;
+                            if (bundle_item(P, item, it)) {
+                                SRT_SU(S_PIX, s) = it.py * P.width + it.px; SRT_SU(S_K, s) = it.n; SRT_SU(S_PXY, s) = it.row;
+                                SRT_SU(S_KEND, s) = it.px | (it.py << 16); SRT_SU(S_FLAGS, s) = kFlagPending;
+                                need = false;
+                            }
+                        }
+                        if (r) need1 = need; else need0 = need;
+                    }
+                }
+                m0 = __ballot_sync(0xFFFFFFFFu, need0); m1 = __ballot_sync(0xFFFFFFFFu, need1);
+            }
+            for (int off = 16; off > 0; off >>= 1) n_retired += __shfl_down_sync(0xFFFFFFFFu, n_retired, off);
+            if (lane == 0 && n_retired) atomicAdd(&ctl->retired, n_retired);
+            bool real = false, odd = false;
+            uint32_t key0 = kInvalidPixel, key1 = kInvalidPixel;
+#pragma unroll 1
+            for (int r = 0; r < 2; ++r) {
+                const uint32_t s = r ? id1 : id0;
+                f3 o = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin), d = mk3(0.0f, 0.0f, 0.0f);   // parked unless a ray is generated
+                BundlePixel bp = {0.0f, 0.0f, 0.0f, -1.0f};
+                uint32_t key = kInvalidPixel;
+                if (s != kRingEmpty) {
+                    const uint32_t pix = SRT_SU(S_PIX, s), n = SRT_SU(S_K, s), pxy = SRT_SU(S_KEND, s);
+                    const uint32_t c = n >> P.bundle_log2;
+                    // the staging row of this pixel chunk must have been released by its previous user: chunk c-1 of
+                    // the same pixel, or the last chunk of the pixel at the same position one band earlier (bands are
+                    // whole block rows: same column, inside the image as well)
+                    bool row_free = true;
+                    if (c != 0u) row_free = *(volatile uint32_t *)&P.done[pix] == (P.done_tag | c);
+                    else if (pix >= P.band_pix) row_free = *(volatile uint32_t *)&P.done[pix - P.band_pix] == (P.done_tag | P.n_chunks);
+                    if (row_free) {
+                        uint64_t rng;
+                        primary_ray<true>(P, pxy & 0xFFFFu, pxy >> 16, pix, P.first_sample + n * P.sample_stride, rng, o, d);
+                        SRT_ST(S_AX, s) = 1.0f; SRT_ST(S_AY, s) = 1.0f; SRT_ST(S_AZ, s) = 1.0f;
+                        SRT_ST(S_LX, s) = 0.0f; SRT_ST(S_LY, s) = 0.0f; SRT_ST(S_LZ, s) = 0.0f;
+                        SRT_SU(S_RNG_LO, s) = (uint32_t)rng; SRT_SU(S_RNG_HI, s) = (uint32_t)(rng >> 32);
+                        SRT_SU(S_FLAGS, s) = 0u;                                      // bounce 0
+                        bp = bundle_pixel(P, pxy & 0xFFFFu, pxy >> 16);
+                        key = pix;
+                        real = true;
+                        odd = odd || bp.eps < 0.0f;
+                    } else pend |= 1u << r;
+                }
+                if (r) { o1 = o; d1 = d; bp1 = bp; key1 = key; } else { o0 = o; d0 = d; bp0 = bp; key0 = key; }
+            }
+            any_real = __any_sync(0xFFFFFFFFu, real);
+            use_bundle = any_real && !__any_sync(0xFFFFFFFFu, odd);
+            // one level-0 scan per run of equal pixels (work items are handed out in pixel order)
+            const uint32_t up0 = __shfl_up_sync(0xFFFFFFFFu, key0, 1), up1 = __shfl_up_sync(0xFFFFFFFFu, key1, 1);
+            const uint32_t last0 = __shfl_sync(0xFFFFFFFFu, key0, 31);
+            heads0 = __ballot_sync(0xFFFFFFFFu, key0 != kInvalidPixel && (lane == 0 || up0 != key0));
+            heads1 = __ballot_sync(0xFFFFFFFFu, key1 != kInvalidPixel && ((lane == 0 ? last0 : up1) != key1));
+            if (P.debug && lane == 0) {
+                atomicAdd(&P.debug[use_bundle ? 2 : 3], 1ull);
+                atomicAdd(&P.debug[4], (unsigned long long)(__popc(heads0) + __popc(heads1)));
+                atomicAdd(&P.debug[5], (unsigned long long)(pend != 0u));
+            }
+        } else if (kind == 0) {
             // ---- 64 slots that need a new primary ray: finish items, fetch new ones (A1) -------
             bool real = false;
 #pragma unroll 1
@@ -515,13 +672,25 @@ render_pool(const __grid_constant__ KernelParams P) {
         ox = pk_make(o0.x, o1.x); oy = pk_make(o0.y, o1.y); oz = pk_make(o0.z, o1.z);
         dx = pk_make(d0.x, d1.x); dy = pk_make(d0.y, d1.y); dz = pk_make(d0.z, d1.z);
         if (any_real) {
-            // level 1 (slab, every sphere) -> level 2 (7-FMA filter on the survivors) -> exact select
-            const SlabRays sr = make_slab_rays(P.slab_axis, ox, oy, oz, dx, dy, dz, P.omax2);
+            // level 1 (slab, every sphere; level 0 = once per pixel bundle for the primary passes of bundle mode)
+            // -> level 2 (7-FMA filter on the survivors) -> exact select
+            const int ip = P.slab_axis == 0 ? 1 : (P.slab_axis == 1 ? 2 : 0), iq = P.slab_axis == 0 ? 2 : (P.slab_axis == 1 ? 0 : 1);
             if (STREAM) {
                 const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
-                stream_pass<W, FMA>(ws, P.ptab, P.scan_table, P.spheres, P.n_pad, P.n_spheres, sr, rays, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+                if (BUNDLE && use_bundle) {
+                    stream_bundle_pass<W, FMA>(P.ptab, P.scan_table, P.spheres, P.n_pad, P.n_spheres, P.cam.pos[ip], P.cam.pos[iq], heads0, heads1, bp0, bp1,
+                                               rays, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+                } else {
+                    const SlabRays sr = make_slab_rays(P.slab_axis, ox, oy, oz, dx, dy, dz, P.omax2);
+                    stream_pass<W, FMA>(ws, P.ptab, P.scan_table, P.spheres, P.n_pad, P.n_spheres, sr, rays, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+                }
             } else {
-                scan_slab_tile(s_slab, P.n_pad, 0u, sr, queue, qn);
+                if (BUNDLE && use_bundle) {
+                    bundle_scan<false>(s_slab, 0u, P.n_pad, P.cam.pos[ip], P.cam.pos[iq], heads0, heads1, bp0, bp1, lane, queue, qn);
+                } else {
+                    const SlabRays sr = make_slab_rays(P.slab_axis, ox, oy, oz, dx, dy, dz, P.omax2);
+                    scan_slab_tile(s_slab, P.n_pad, 0u, sr, queue, qn);
+                }
                 const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
                 const FetchScanResident fetch_scan = {s_scan};
                 refine_queue(fetch_scan, queue, qn, rays);
@@ -538,7 +707,7 @@ render_pool(const __grid_constant__ KernelParams P) {
             const uint32_t s = r ? id1 : id0;
             const bool waits = ((pend >> r) & 1u) != 0u;
             const bool valid = s != kRingEmpty && !waits;
-            bool ended = false;
+            bool ended = false, folds = false;
             if (valid) {
                 const Hit h = r ? h1 : h0;
                 f3 o = r ? o1 : o0, d = r ? d1 : d0;
@@ -548,7 +717,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                 f3 atten = mk3(SRT_ST(S_AX, s), SRT_ST(S_AY, s), SRT_ST(S_AZ, s));
                 f3 out = mk3(SRT_ST(S_LX, s), SRT_ST(S_LY, s), SRT_ST(S_LZ, s));
                 uint64_t rng = (uint64_t)SRT_SU(S_RNG_LO, s) | ((uint64_t)SRT_SU(S_RNG_HI, s) << 32);
-                if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
+                if (bounce == 0 && P.tap_t != nullptr && k == (BUNDLE ? 0u : P.first_sample)) {
                     const uint32_t pix = SRT_SU(S_PIX, s);
                     P.tap_t[pix] = h.t;
                     P.tap_prim[pix] = h.prim;
@@ -556,7 +725,13 @@ render_pool(const __grid_constant__ KernelParams P) {
                 float4 sp = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (h.hit) sp = STREAM ? __ldg(P.spheres + h.prim) : s_scan[h.prim];   // centre only; .w is not used by shading
                 ended = shade_scatter<true>(P, h, sp, o, d, atten, out, rng, bounce);
-                if (ended) {
+                if (BUNDLE && ended) {
+                    // stage the sample (S_K holds its ordinal); the slot that delivers the chunk's last one folds the chunk
+                    const uint32_t row = SRT_SU(S_PXY, s), c = k >> P.bundle_log2;
+                    P.stage[((size_t)row << P.bundle_log2) + (k & ((1u << P.bundle_log2) - 1u))] = make_float4(out.x, out.y, out.z, 0.0f);
+                    __threadfence();
+                    folds = atomicAdd(&P.cnt[row], 1u) + 1u == min(1u << P.bundle_log2, P.n_samples - (c << P.bundle_log2));
+                } else if (ended) {
                     const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, s), SRT_ST(S_MY, s), SRT_ST(S_MZ, s)), out, k);
                     SRT_ST(S_MX, s) = mean.x; SRT_ST(S_MY, s) = mean.y; SRT_ST(S_MZ, s) = mean.z;
                     SRT_SU(S_K, s) = k + P.sample_stride;
@@ -567,6 +742,15 @@ render_pool(const __grid_constant__ KernelParams P) {
                     SRT_ST(S_AX, s) = atten.x; SRT_ST(S_AY, s) = atten.y; SRT_ST(S_AZ, s) = atten.z;
                     SRT_ST(S_LX, s) = out.x; SRT_ST(S_LY, s) = out.y; SRT_ST(S_LZ, s) = out.z;
                     SRT_SU(S_FLAGS, s) = bounce;
+                }
+            }
+            if (BUNDLE) {
+                unsigned fm = __ballot_sync(0xFFFFFFFFu, folds);
+                while (fm) {
+                    const int src = __ffs(fm) - 1;
+                    fm &= fm - 1u;
+                    const uint32_t fs = __shfl_sync(0xFFFFFFFFu, s, src);
+                    fold_bundle(P, SRT_SU(S_PIX, fs), SRT_SU(S_PXY, fs), SRT_SU(S_K, fs) >> P.bundle_log2, lane);
                 }
             }
             pool_push(ctl, ring0, RCAP - 1u, 0, (valid && ended) || waits, s, lane);
@@ -595,7 +779,7 @@ render_pool(const __grid_constant__ KernelParams P) {
 template <int W, bool FMA>
 __global__ void __launch_bounds__(kBlockThreads)
 audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counters) {
-    unsigned long long n_tests = 0, n_hits = 0, n_cand = 0, n_viol = 0, n_slab = 0;
+    unsigned long long n_tests = 0, n_hits = 0, n_cand = 0, n_viol = 0, n_slab = 0, n_btests = 0, n_bcand = 0, n_bviol = 0;
     const uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x;
     if (pix < P.width * P.height) {
         const uint32_t px = pix % P.width, py = pix / P.width;
@@ -604,6 +788,8 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
             f3 o, d, atten = mk3(1.0f, 1.0f, 1.0f), out = mk3(0.0f, 0.0f, 0.0f);
             uint32_t bounce = 0;
             primary_ray(P, px, py, pix, k, rng, o, d);
+            const BundlePixel bp = bundle_pixel(P, px, py);            // level 0 of bundle mode: primary rays only
+            const int ip = P.slab_axis == 0 ? 1 : (P.slab_axis == 1 ? 2 : 0), iq = P.slab_axis == 0 ? 2 : (P.slab_axis == 1 ? 0 : 1);
             for (;;) {
                 const FilterRay f = filter_ray(o.x, o.y, o.z, d.x, d.y, d.z);
                 const pk2 p2ox = pk_make(f.p2ox, f.p2ox), p2oy = pk_make(f.p2oy, f.p2oy), p2oz = pk_make(f.p2oz, f.p2oz);
@@ -627,6 +813,12 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
                     n_slab += slab ? 1 : 0;
                     n_cand += (slab && mask) ? 1 : 0;
                     n_viol += (exact && !(slab && mask)) ? 1 : 0;
+                    if (bounce == 0 && !(bp.eps < 0.0f)) {             // a pixel with eps < 0 takes the per-ray scan
+                        const bool bund = bundle_test(cp, cq, i < P.n_spheres ? slab_radius(s.w, s.x, s.y, s.z, P.omax) : -1.0f, P.cam.pos[ip], P.cam.pos[iq], bp);
+                        n_btests += 1;
+                        n_bcand += bund ? 1 : 0;
+                        n_bviol += (exact && !bund) ? 1 : 0;
+                    }
                 }
                 Hit h;
                 if (W == 1) h = intersect_scalar(P.spheres, P.n_pad, P.n_spheres, o, d);
@@ -643,6 +835,9 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
         n_cand += __shfl_down_sync(0xFFFFFFFFu, n_cand, off);
         n_viol += __shfl_down_sync(0xFFFFFFFFu, n_viol, off);
         n_slab += __shfl_down_sync(0xFFFFFFFFu, n_slab, off);
+        n_btests += __shfl_down_sync(0xFFFFFFFFu, n_btests, off);
+        n_bcand += __shfl_down_sync(0xFFFFFFFFu, n_bcand, off);
+        n_bviol += __shfl_down_sync(0xFFFFFFFFu, n_bviol, off);
     }
     if ((threadIdx.x & 31u) == 0) {
         atomicAdd(&counters[0], n_tests);
@@ -650,6 +845,9 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
         atomicAdd(&counters[2], n_cand);
         atomicAdd(&counters[3], n_viol);
         atomicAdd(&counters[4], n_slab);
+        atomicAdd(&counters[5], n_btests);
+        atomicAdd(&counters[6], n_bcand);
+        atomicAdd(&counters[7], n_bviol);
     }
 }
 
@@ -721,6 +919,13 @@ struct srt_backend {
     int slab_axis = 1;                   // axis contained in the slab planes: least spread of the centres
     double omax_scene = 0.0;             // >= |C| + r of every sphere (bound on secondary-ray origins)
     uint32_t pool_chunk = 0;             // samples per work item, 0 = kPoolChunkSamples (SRT_POOL_CHUNK)
+    int bundle = 1;                      // bundle mode of the pool kernel for launches of >= kBundleMinSamples samples (SRT_BUNDLE=0: off)
+    float4 *d_stage = nullptr;           // bundle mode: staging rows of the pixels in flight (KernelParams::stage)
+    uint32_t *d_cnt = nullptr;           // bundle mode: samples staged per row
+    size_t stage_bytes = 0, cnt_rows = 0;
+    float2 *d_fold_w = nullptr;          // bundle mode: running-mean weights of the launch's samples
+    uint32_t fold_w_cap = 0;
+    std::vector<float2> h_fold_w;
     unsigned long long *h_rays = nullptr;   // pinned
     bool in_flight = false;
     uint64_t launches = 0;
@@ -781,19 +986,23 @@ constexpr int kPoolThreads = 256;           // streamed kernel: 2 CTAs of 256 th
 constexpr int kPoolMinBlocks = 2;
 constexpr uint32_t kPoolChunkSamples = 1;   // samples per pool work item (measured best: 1; SRT_POOL_CHUNK overrides)
 constexpr int kPoolResidentThreads[3] = {896, 512, 256};
-template <int THREADS, int MINB, bool STREAM>
+template <int THREADS, int MINB, bool STREAM, bool BUNDLE>
 static render_kernel_t pick_pool_kernel_cfg(const srt_scene_options &o) {
-    if (o.lane_width == 1) return render_pool<1, false, THREADS, MINB, STREAM>;
-    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, THREADS, MINB, STREAM> : render_pool<4, false, THREADS, MINB, STREAM>;
-    return o.fma_dot ? render_pool<8, true, THREADS, MINB, STREAM> : render_pool<8, false, THREADS, MINB, STREAM>;
+    if (o.lane_width == 1) return render_pool<1, false, THREADS, MINB, STREAM, BUNDLE>;
+    if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, THREADS, MINB, STREAM, BUNDLE> : render_pool<4, false, THREADS, MINB, STREAM, BUNDLE>;
+    return o.fma_dot ? render_pool<8, true, THREADS, MINB, STREAM, BUNDLE> : render_pool<8, false, THREADS, MINB, STREAM, BUNDLE>;
 }
-static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream, int threads) {
-    if (stream && threads == 768 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 768, 1, true>;   // experiment
-    if (stream && threads == 512 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 512, 1, true>;   // experiment
-    if (stream) return pick_pool_kernel_cfg<kPoolThreads, kPoolMinBlocks, true>(o);
-    if (threads == 896) return pick_pool_kernel_cfg<896, 1, false>(o);
-    if (threads == 512) return pick_pool_kernel_cfg<512, 1, false>(o);
-    return pick_pool_kernel_cfg<256, 1, false>(o);
+template <bool BUNDLE>
+static render_kernel_t pick_pool_kernel_b(const srt_scene_options &o, bool stream, int threads) {
+    if (stream && threads == 768 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 768, 1, true, BUNDLE>;   // experiment
+    if (stream && threads == 512 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 512, 1, true, BUNDLE>;   // experiment
+    if (stream) return pick_pool_kernel_cfg<kPoolThreads, kPoolMinBlocks, true, BUNDLE>(o);
+    if (threads == 896) return pick_pool_kernel_cfg<896, 1, false, BUNDLE>(o);
+    if (threads == 512) return pick_pool_kernel_cfg<512, 1, false, BUNDLE>(o);
+    return pick_pool_kernel_cfg<256, 1, false, BUNDLE>(o);
+}
+static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream, int threads, bool bundle) {
+    return bundle ? pick_pool_kernel_b<true>(o, stream, threads) : pick_pool_kernel_b<false>(o, stream, threads);
 }
 static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
     const size_t ns = 64u * (threads / 32 + kPoolSpareBatches), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
@@ -804,6 +1013,38 @@ static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
 }
 static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
     return (size_t)n_pad * (sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * 2 * threads * sizeof(float);
+}
+
+// Bundle mode (srt_bundle.cuh).
+constexpr uint32_t kBundleMinSamples = 8;        // launches with fewer samples keep (chunk, pixel) work items
+constexpr uint32_t kBundleBandItemsLog2 = 21;
+static MagicDiv make_magic(uint32_t d) {          // srt_device.cuh: x / d for x < 2^30
+    uint32_t l = 0;
+    while ((1ull << l) < d) ++l;
+    MagicDiv m;
+    m.m = (uint32_t)((((uint64_t)1 << (30 + l)) + d - 1) / d);
+    m.sh = 30 + l;
+    return m;
+}    // work items per band and chunk: 2 Mi >> paths in flight (148 x 1,920)
+// rho >= |F(j)_pq - F(0)_pq| for every jitter j in [-0.5, 0.5]^2 of any pixel (film units, kept axes p, q), plus the
+// fp32 rounding of both film-point evaluations (main.cpp:378-384: <= u (2 |fc_i| + 12) per component).  0 = do not bundle.
+static double bundle_footprint(const srt_camera *cam, uint32_t width, uint32_t height, int axis) {
+    const int ip = axis == 0 ? 1 : (axis == 1 ? 2 : 0), iq = axis == 0 ? 2 : (axis == 1 ? 0 : 1);
+    const double fw = cam->film_w, fh = cam->film_h;
+    double nx = 0, ny = 0, mag = 0;
+    for (int i = 0; i < 3; ++i) {
+        nx += (double)cam->camera_x[i] * cam->camera_x[i];
+        ny += (double)cam->camera_y[i] * cam->camera_y[i];
+        mag = std::max({mag, fabs((double)cam->film_center[i]), fabs((double)cam->camera_position[i])});
+    }
+    if (!(fw > 0 && fw <= 4 && fh > 0 && fh <= 4 && nx <= 4 && ny <= 4 && mag < 1e6)) return 0.0;   // NaN fails too
+    const double dax = fw / (2.0 * width), day = fh / (2.0 * height);
+    const double xp = cam->camera_x[ip], xq = cam->camera_x[iq], yp = cam->camera_y[ip], yq = cam->camera_y[iq];
+    const double a2 = dax * dax * (xp * xp + xq * xq), b2 = day * day * (yp * yp + yq * yq), cross = 2.0 * dax * day * fabs(xp * yp + xq * yq);
+    const double u = 5.9604644775390625e-08;
+    const double fp_err = 8.0 * u * (fabs((double)cam->film_center[ip]) + fabs((double)cam->film_center[iq]) +
+                                     fabs((double)cam->camera_position[ip]) + fabs((double)cam->camera_position[iq]) + 16.0);
+    return sqrt(a2 + b2 + cross) * 1.001 + fp_err;
 }
 
 extern "C" {
@@ -848,7 +1089,7 @@ void srt_destroy(srt_backend *b) {
     cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
     cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
     cudaFree(b->d_counters);
-    cudaFree(b->d_done);
+    cudaFree(b->d_done); cudaFree(b->d_stage); cudaFree(b->d_cnt); cudaFree(b->d_fold_w);
     if (b->h_rays) cudaFreeHost(b->h_rays);
     if (b->ev_start) cudaEventDestroy(b->ev_start);
     if (b->ev_stop) cudaEventDestroy(b->ev_stop);
@@ -956,6 +1197,7 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
     if (const char *v = getenv("SRT_KERNEL_VARIANT")) b->variant = atoi(v);
     b->pool_chunk = 0;
     if (const char *v = getenv("SRT_POOL_CHUNK")) b->pool_chunk = (uint32_t)std::max(0, atoi(v));
+    if (const char *v = getenv("SRT_BUNDLE")) b->bundle = atoi(v);
     // Path start-up costs the whole warp ~200 issue slots however few lanes need it.  For
     // tiny scenes (intersection pass cheaper than that) a warp therefore refills only once
     // all its lanes are idle, which also keeps its primary rays coherent; measured on B200:
@@ -1043,6 +1285,9 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.width = b->width;
     P.height = b->height;
     P.blocks_x = (b->width + 7u) / 8u;
+    P.div_bx = make_magic(P.blocks_x);
+    P.two_over_w = 2.0f / (float)b->width;
+    P.two_over_h = 2.0f / (float)b->height;
     P.total_items = P.blocks_x * ((b->height + 3u) / 4u) * 32u;
     P.first_sample = args->first_sample;
     P.n_samples = args->n_samples;
@@ -1105,6 +1350,9 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         b->tap_valid = true;
     }
 
+    bool use_bundle = false;
+    const bool pool_debug = getenv("SRT_POOL_DEBUG") != nullptr;
+    if (!pool_debug) P.debug = nullptr;
     if (pool) {
         // work items = (sample chunk, pixel), chunk-major.  A pixel's chunks are folded in order through
         // done[pix]; short chunks keep the end of the launch short (few slots left with many samples to go).
@@ -1112,22 +1360,83 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
             SRT_CUDA(b, cudaMalloc(&b->d_done, (size_t)b->width * b->height * sizeof(uint32_t)));
             SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
         }
+        // bundle mode (srt_bundle.cuh): work items are single samples, 2^bundle_log2 consecutive samples of a pixel
+        // are consecutive items; needs a sane pinhole camera (the footprint bound below) and 32-bit item indices
+        bool bundle = false;
+        uint32_t blog = 0;
+        if (b->bundle && args->n_samples >= kBundleMinSamples && !b->pool_chunk) {
+            while (blog < 6u && (2u << blog) <= args->n_samples) ++blog;                 // S = min(64, 2^floor(log2 n))
+            if (b->bundle > 1) blog = std::min<uint32_t>(blog, (uint32_t)b->bundle);     // SRT_BUNDLE=k (k >= 2): S <= 2^k (tests)
+            const uint64_t S = 1ull << blog, n_chunks = (args->n_samples + S - 1) / S;
+            const double rho = bundle_footprint(cam, b->width, b->height, P.slab_axis);
+            if (rho > 0.0 && n_chunks <= 4095 && (uint64_t)P.items_per_gen * n_chunks * S < 0xF0000000ull) {
+                bundle = true;
+                P.bundle_log2 = blog;
+                P.n_chunks = (uint32_t)n_chunks;
+                // bands of whole block rows, ~2^21 work items per band and chunk (SRT_BUNDLE_BAND_ROWS: tests, tiny bands)
+                const uint32_t row_items = P.blocks_x * 32u, blocks_y = P.items_per_gen / row_items;
+                uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)(((1ull << kBundleBandItemsLog2) >> blog) / row_items));
+                if (const char *v = getenv("SRT_BUNDLE_BAND_ROWS")) band_rows = (uint32_t)std::max(1, atoi(v));
+                band_rows = std::min(band_rows, blocks_y);
+                P.n_bands = (blocks_y + band_rows - 1) / band_rows;
+                P.band_items = band_rows * row_items;
+                P.band_last = P.items_per_gen - (P.n_bands - 1) * P.band_items;
+                P.band_pix = band_rows * 4u * b->width;
+                P.div_full = make_magic(P.band_items * P.n_chunks);
+                P.div_band = make_magic(P.band_items);
+                P.div_last = make_magic(P.band_last);
+                P.bundle_rho = (float)rho;
+                P.total_items = (uint32_t)((uint64_t)P.items_per_gen * n_chunks * S);
+                const size_t rows = P.band_items, need = rows * S * sizeof(float4);
+                if (need > b->stage_bytes || rows > b->cnt_rows) {
+                    cudaFree(b->d_stage); cudaFree(b->d_cnt);
+                    b->d_stage = nullptr; b->d_cnt = nullptr; b->stage_bytes = 0; b->cnt_rows = 0;
+                    SRT_CUDA(b, cudaMalloc(&b->d_stage, need));
+                    SRT_CUDA(b, cudaMalloc(&b->d_cnt, rows * sizeof(uint32_t)));
+                    b->stage_bytes = need;
+                    b->cnt_rows = rows;
+                }
+                SRT_CUDA(b, cudaMemsetAsync(b->d_cnt, 0, rows * sizeof(uint32_t), b->stream));
+                P.stage = b->d_stage;
+                P.cnt = b->d_cnt;
+                if (args->accum_mode == SRT_ACCUM_MEAN) {                 // A8 weights of the launch's samples (main.cpp:484-487)
+                    if (args->n_samples > b->fold_w_cap) {
+                        cudaFree(b->d_fold_w);
+                        b->d_fold_w = nullptr; b->fold_w_cap = 0;
+                        SRT_CUDA(b, cudaMalloc(&b->d_fold_w, (size_t)args->n_samples * sizeof(float2)));
+                        b->fold_w_cap = args->n_samples;
+                    }
+                    b->h_fold_w.resize(args->n_samples);
+                    for (uint32_t i = 0; i < args->n_samples; ++i) {
+                        const uint32_t k = args->first_sample + i * args->sample_stride;
+                        const float total = (float)(k + 1u);
+                        b->h_fold_w[i] = make_float2(1.0f / total, (float)k / total);
+                    }
+                    SRT_CUDA(b, cudaMemcpyAsync(b->d_fold_w, b->h_fold_w.data(), (size_t)args->n_samples * sizeof(float2), cudaMemcpyHostToDevice, b->stream));
+                    P.fold_w = b->d_fold_w;
+                }
+            }
+        }
+        use_bundle = bundle;
+        if (!bundle) {
         uint32_t chunk = b->pool_chunk ? b->pool_chunk : kPoolChunkSamples;
         const uint32_t max_chunks = std::min<uint32_t>(4095u, 0xF0000000u / P.items_per_gen);
         if ((args->n_samples + chunk - 1) / chunk > max_chunks) chunk = (args->n_samples + max_chunks - 1) / max_chunks;
         const uint32_t n_chunks = (args->n_samples + chunk - 1) / chunk;
         P.chunk_span = chunk * args->sample_stride;
         P.total_items = P.items_per_gen * n_chunks;
+        P.n_chunks = n_chunks;
+        }
         P.done = b->d_done;
         P.done_tag = (uint32_t)((b->launches + 1) & 0xFFFFFu) << 12;
-        if (P.done_tag == 0u && n_chunks > 1u)   // sequence wrapped: forget counts of 2^20 launches ago
+        if (P.done_tag == 0u && P.n_chunks > 1u)   // sequence wrapped: forget counts of 2^20 launches ago
             SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
     }
     if (stream || !pool_res_fit) {
         pool_threads = kPoolThreads;
         if (const char *v = getenv("SRT_STREAM_THREADS")) { const int t = atoi(v); if ((t == 512 || t == 768) && b->opt.lane_width == 8 && b->opt.fma_dot) pool_threads = t; }
     }
-    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
+    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, use_bundle) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
     const int threads = pool ? pool_threads : pairs ? pc.threads : kBlockThreads;
     const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1158,11 +1467,12 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     SRT_CUDA(b, cudaMemcpyAsync(b->h_rays, b->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, b->stream));
     b->launches += 1;
     b->in_flight = true;
-    if (getenv("SRT_POOL_DEBUG")) {
-        unsigned long long dbg[2] = {0, 0};
+    if (pool_debug) {
+        unsigned long long dbg[6] = {0, 0, 0, 0, 0, 0};
         cudaStreamSynchronize(b->stream);
         cudaMemcpy(dbg, b->d_counters + 16, sizeof(dbg), cudaMemcpyDeviceToHost);
-        fprintf(stderr, "[srt pool] acquire spins: steady %llu, tail %llu\n", dbg[0], dbg[1]);
+        fprintf(stderr, "[srt pool] acquire spins: steady %llu, tail %llu; primary passes: bundled %llu, per-ray %llu, pixel runs %llu, lane-0 waits %llu\n",
+                dbg[0], dbg[1], dbg[2], dbg[3], dbg[4], dbg[5]);
     }
     return SRT_OK;
 }
@@ -1190,13 +1500,14 @@ int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays) {
     return SRT_OK;
 }
 
-int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_args *args, uint64_t out_counts[5]) {
+int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_args *args, uint64_t out_counts[8]) {
     if (!b) return SRT_ERR_INVALID;
     if (!out_counts) return fail(b, SRT_ERR_INVALID, "srt_filter_audit: null output");
     KernelParams P;
     int rc = make_params(b, cam, args, "srt_filter_audit", P);
     if (rc) return rc;
     if (args->sample_stride != 1) return fail(b, SRT_ERR_INVALID, "srt_filter_audit: sample_stride must be 1");
+    P.bundle_rho = (float)bundle_footprint(cam, b->width, b->height, P.slab_axis);
     SRT_CUDA(b, cudaSetDevice(b->device));
     rc = drain(b);
     if (rc) return rc;
@@ -1212,12 +1523,12 @@ int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_arg
     else if (o.fma_dot) audit_filter<8, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     else audit_filter<8, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     cudaError_t e = cudaGetLastError();
-    unsigned long long h[5] = {0, 0, 0, 0, 0};
+    unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, b->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
     cudaFree(d_cnt);
     if (e != cudaSuccess) return fail(b, SRT_ERR_CUDA, std::string("srt_filter_audit: ") + cudaGetErrorString(e));
-    for (int i = 0; i < 5; ++i) out_counts[i] = h[i];
+    for (int i = 0; i < 8; ++i) out_counts[i] = h[i];
     b->launches += 1;
     return SRT_OK;
 }

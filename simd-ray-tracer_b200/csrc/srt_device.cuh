@@ -115,6 +115,12 @@ struct DevCamera {
     float film_w, film_h;
 };
 
+// x / d for a divisor fixed per launch and x < 2^30: q = (x * m) >> sh with m = ceil(2^(30+l) / d), 2^l >= d
+// (Granlund-Montgomery; 3 instructions instead of the ~20 of a 32-bit division -- the pool kernel's hot code
+// has to stay inside the 32 KB instruction cache).
+struct MagicDiv { uint32_t m, sh; };
+__host__ __device__ __forceinline__ uint32_t magic_div(uint32_t x, MagicDiv d) { return (uint32_t)(((uint64_t)x * d.m) >> d.sh); }
+
 struct KernelParams {
     const float4 *spheres;       // n_pad entries {cx,cy,cz,r2}, zero spheres as padding (never hit);
                                  // packed kernels: pair layout {x0,x1,y0,y1},{z0,z1,r2_0,r2_1}
@@ -129,6 +135,7 @@ struct KernelParams {
     DevCamera cam;
     uint32_t width, height;
     uint32_t blocks_x;           // 8x4 pixel blocks per row
+    MagicDiv div_bx;             // / blocks_x
     uint32_t total_items;        // blocks_x * blocks_y * 32
     uint32_t first_sample, n_samples, sample_stride, accum_mode;
     uint64_t stream_base;
@@ -146,6 +153,22 @@ struct KernelParams {
     uint32_t chunk_span;         // samples per chunk * sample_stride
     uint32_t items_per_gen;      // blocks_x * blocks_y * 32; pool: total_items = items_per_gen * chunks
     uint32_t regen_threshold;    // start new paths once this many lanes of a warp are idle
+    // pool kernel, bundle mode: a work item is ONE sample; 2^bundle_log2 consecutive samples of a
+    // pixel are consecutive items, so a primary warp pass holds all samples of one (or a few) pixels and the
+    // level-1 slab test is done once per (pixel, sphere) for the whole bundle.  Finished samples are staged and
+    // folded into the running mean in sample order by the slot that delivers the chunk's last one.
+    uint32_t bundle_log2;        // 0: bundle mode off
+    uint32_t n_chunks;           // sample chunks per pixel = ceil(n_samples / 2^bundle_log2)
+    uint32_t band_items;         // pixels are processed in bands of whole 8x4-block rows: pixel items per band
+    uint32_t band_last;          // pixel items of the last band (<= band_items)
+    uint32_t n_bands;
+    uint32_t band_pix;           // pixel-index distance of the same pixel position one band earlier (4 * block rows * width)
+    MagicDiv div_full, div_band, div_last;   // / (band_items * n_chunks), / band_items, / band_last
+    float bundle_rho;            // bound on |F(j) - F(0)| over a pixel's jitter footprint, film units, kept axes (host, double)
+    float two_over_w, two_over_h;
+    float4 *stage;               // [band_items][2^bundle_log2] finished samples {r,g,b,-} of the pixels in flight
+    uint32_t *cnt;               // [band_items] samples staged for the row's current chunk
+    const float2 *fold_w;        // [n_samples] {1/N, (N-1)/N} of main.cpp:484-487 for the launch's samples (IEEE, host)
     float neg_one, one;          // -1.0f / +1.0f, deliberately opaque to the compiler (srt_packed.cuh)
 };
 

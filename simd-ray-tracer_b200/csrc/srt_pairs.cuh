@@ -101,6 +101,10 @@ __device__ __forceinline__ FilterRay filter_ray(float ox, float oy, float oz, fl
     return f;
 }
 
+__device__ __noinline__ FilterRay filter_ray_call(float ox, float oy, float oz, float dx, float dy, float dz) {
+    return filter_ray(ox, oy, oz, dx, dy, dz);
+}
+
 // mask |= bit  iff  za > ooa || zb > oob : FSETP, FSETP.OR, predicated LOP3.
 __device__ __forceinline__ void filter_mark(uint32_t &mask, float za, float ooa, float zb, float oob, uint32_t bit) {
     asm("{\n\t.reg .pred p;\n\tsetp.gt.f32 p, %1, %2;\n\tsetp.gt.or.f32 p, %3, %4, p;\n\t@p or.b32 %0, %0, %5;\n\t}"
@@ -140,7 +144,7 @@ __device__ __forceinline__ ScanRays make_scan_rays(pk2 ox, pk2 oy, pk2 oz, pk2 d
     float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
     pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
     pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
-    const FilterRay fa = filter_ray(oxa, oya, oza, dxa, dya, dza), fb = filter_ray(oxb, oyb, ozb, dxb, dyb, dzb);
+    const FilterRay fa = filter_ray_call(oxa, oya, oza, dxa, dya, dza), fb = filter_ray_call(oxb, oyb, ozb, dxb, dyb, dzb);
     ScanRays r;
     r.p2ox = pk_make(fa.p2ox, fb.p2ox); r.p2oy = pk_make(fa.p2oy, fb.p2oy); r.p2oz = pk_make(fa.p2oz, fb.p2oz);
     r.dx = pk_make(fa.dx, fb.dx); r.dy = pk_make(fa.dy, fb.dy); r.dz = pk_make(fa.dz, fb.dz);
@@ -252,7 +256,7 @@ __device__ __forceinline__ void scan_tile(const float4 *__restrict__ tile, uint3
 // arithmetic (select).  Every sphere is still tested against every ray.
 // Soundness: a reference hit has |w - D tau| < r(1+2.7u) + 6.3u|w|, and
 // (w - D tau).U* = w.U* for the real unit normal U*; U, O.U and a are evaluated with errors
-// <= 7.4u(|C|+|O|) in total.  r' = r(1+16u) + 32u(|C| + Omax) + 1e-30 covers both as long as
+// <= 7.4u(|C|+|O|) in total.  r' = r(1+32u) + 32u(|C| + Omax) + 1e-30 covers both as long as
 // |O| <= Omax (the launch's bound on ray origins); a ray with a larger origin, a near-axis
 // direction (|(D_p, D_q)|^2 < 1e-16) or a NaN takes U = 0, O.U = 0: every sphere is a candidate.
 // Parked halves (O = kIdleOrigin) take -O.U = -inf: no candidates.  Padding has r' = -1.
@@ -277,18 +281,23 @@ __device__ __forceinline__ SlabRay slab_ray(int axis, float ox, float oy, float 
 // r' of one sphere for a launch whose ray origins satisfy |O| <= omax.
 __device__ __forceinline__ float slab_radius(float r2, float cx, float cy, float cz, float omax) {
     const float c = __fsqrt_rn(__fmaf_rn(cz, cz, __fmaf_rn(cy, cy, __fmul_rn(cx, cx))));
-    return __fmaf_rn(32.0f * kFilterU, __fadd_rn(c, omax), __fmaf_rn(__fsqrt_rn(r2), 1.0f + 16.0f * kFilterU, 1.0e-30f));
+    return __fmaf_rn(32.0f * kFilterU, __fadd_rn(c, omax), __fmaf_rn(__fsqrt_rn(r2), 1.0f + 32.0f * kFilterU, 1.0e-30f));
 }
 __device__ __forceinline__ bool slab_test(float cp, float cq, float rr, const SlabRay &r) {
     return fabsf(__fmaf_rn(cp, r.up, __fmaf_rn(cq, r.uq, r.nou))) <= rr;
 }
 
+// Out-of-line copies for the kernels that build the constants of two rays per pass: one copy of the IEEE
+// square root / divisions instead of two (instruction-cache footprint).
+__device__ __noinline__ SlabRay slab_ray_call(int axis, float ox, float oy, float oz, float dx, float dy, float dz, float omax2) {
+    return slab_ray(axis, ox, oy, oz, dx, dy, dz, omax2);
+}
 struct SlabRays { pk2 up, uq, nou; };
 __device__ __forceinline__ SlabRays make_slab_rays(int axis, pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz, float omax2) {
     float oxa, oxb, oya, oyb, oza, ozb, dxa, dxb, dya, dyb, dza, dzb;
     pk_split(ox, oxa, oxb); pk_split(oy, oya, oyb); pk_split(oz, oza, ozb);
     pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
-    const SlabRay a = slab_ray(axis, oxa, oya, oza, dxa, dya, dza, omax2), b = slab_ray(axis, oxb, oyb, ozb, dxb, dyb, dzb, omax2);
+    const SlabRay a = slab_ray_call(axis, oxa, oya, oza, dxa, dya, dza, omax2), b = slab_ray_call(axis, oxb, oyb, ozb, dxb, dyb, dzb, omax2);
     SlabRays r;
     r.up = pk_make(a.up, b.up); r.uq = pk_make(a.uq, b.uq); r.nou = pk_make(a.nou, b.nou);
     return r;

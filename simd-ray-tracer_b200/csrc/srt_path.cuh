@@ -13,7 +13,7 @@ constexpr uint32_t kInvalidPixel = 0xFFFFFFFFu;
 // material branch diverge less).  Returns false for items outside the image.
 __device__ __forceinline__ bool item_to_pixel(const KernelParams &P, uint32_t item, uint32_t &px, uint32_t &py) {
     const uint32_t blk = item >> 5, in = item & 31u;
-    const uint32_t bx = blk % P.blocks_x, by = blk / P.blocks_x;
+    const uint32_t by = magic_div(blk, P.div_bx), bx = blk - by * P.blocks_x;
     px = bx * 8u + (in & 7u);
     py = by * 4u + (in >> 3);
     return px < P.width && py < P.height;

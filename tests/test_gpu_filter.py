@@ -60,7 +60,7 @@ def test_filter_audit_scenes(backend, srt, scene, mode):
     backend.resize(w, h)
     a = backend.filter_audit(cam, 0, 2)
     assert a["tests"] > 0 and a["hits"] > 0
-    assert a["violations"] == 0, a
+    assert a["violations"] == 0 and a["bundle_violations"] == 0, a
     assert a["candidates"] >= a["hits"]
     assert a["candidates"] < 4 * a["hits"] + a["tests"] // 500, a   # the filter stays selective
 
@@ -83,7 +83,7 @@ def test_filter_audit_large_coordinates(backend, srt, oracle, off):
     backend.set_scene(s2, sky, 8, True)
     backend.resize(w, h)
     a = backend.filter_audit(c2, 0, 2)
-    assert a["violations"] == 0, a
+    assert a["violations"] == 0 and a["bundle_violations"] == 0, a
     o = oracle.render(s2, sky, 8, 1, c2, w, h, 0, 2)
     g = _render(backend, s2, sky, 8, 1, c2, w, h, 2)
     assert _same(o, g) == {}
@@ -115,7 +115,7 @@ def test_filter_audit_tiny_far_spheres(backend, srt, oracle):
         backend.set_scene(sp, True, W, bool(fma))
         backend.resize(w, h)
         a = backend.filter_audit(cam, 0, 2)
-        assert a["hits"] > 0 and a["violations"] == 0, (W, fma, a)
+        assert a["hits"] > 0 and a["violations"] == 0 and a["bundle_violations"] == 0, (W, fma, a)
         o = oracle.render(sp, True, W, fma, cam, w, h, 0, 2)
         g = _render(backend, sp, True, W, fma, cam, w, h, 2)
         assert _same(o, g) == {}, (W, fma)
@@ -180,7 +180,7 @@ def test_streamed_64k_scene_vs_oracle(backend, srt, oracle, mode):
     backend.set_scene(spheres, sky, W, bool(fma))
     backend.resize(16, 9)
     a = backend.filter_audit(srt.host_camera(4, 16, 9, hdr), 0, 1)
-    assert a["hits"] > 0 and a["violations"] == 0, a
+    assert a["hits"] > 0 and a["violations"] == 0 and a["bundle_violations"] == 0, a
 
 
 def test_streamed_ragged_scene_sizes(backend, srt, oracle, monkeypatch):
@@ -225,7 +225,7 @@ def test_nested_and_tied_spheres(backend, srt, oracle, mode):
     assert _same(o, g) == {}
     backend.set_scene(sp, True, W, bool(fma))
     a = backend.filter_audit(cam, 0, 2)
-    assert a["violations"] == 0, a
+    assert a["violations"] == 0 and a["bundle_violations"] == 0, a
 
 
 @pytest.mark.parametrize("chunk", ["", "1", "3", "1000"])
@@ -320,7 +320,7 @@ def test_slab_degenerate_rays_and_far_camera(backend, srt, oracle, mode):
         g = _render(backend, sp, True, W, fma, cam, w, h, 2)
         assert _same(o, g) == {}
         a = backend.filter_audit(cam, 0, 1)
-        assert a["violations"] == 0, a
+        assert a["violations"] == 0 and a["bundle_violations"] == 0, a
 
 
 def test_full_size_4k_properties(srt, monkeypatch):
