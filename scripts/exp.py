@@ -4,6 +4,8 @@ import importlib, os, sys, json
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 srt = importlib.import_module("simd-ray-tracer_b200")
+if os.environ.get("SRT_EXP_LIB"):
+    srt.LIB_PATH = os.path.join(ROOT, os.environ["SRT_EXP_LIB"])   # an experimental build of the library
 def run(name, scene, w, h, spp, env, reps=3):
     saved = {}
     for k, v in env.items():

@@ -142,8 +142,9 @@ render_paths(const __grid_constant__ KernelParams P) {
 // the registers of the hot loop hold nothing but the two packed rays and its temporaries, and
 // the regenerate / shade phases are plain run-time loops over the two slots.
 // ------------------------------------------------------------------------------------------
-enum : int { S_OX, S_OY, S_OZ, S_DX, S_DY, S_DZ, S_AX, S_AY, S_AZ, S_LX, S_LY, S_LZ, S_MX, S_MY, S_MZ,
-             S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_KEND, S_COUNT };
+enum : int { S_OX, S_OY, S_OZ, S_DX, S_DY, S_DZ, S_AX, S_AY, S_AZ, S_LX, S_LY, S_LZ,
+             S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_KEND, S_MX, S_MY, S_MZ, S_COUNT };
+constexpr int kBundleFields = S_COUNT - 3;   // bundle mode keeps no running mean in the slot (S_MX..S_MZ): 23 KB more L1 for the queues
 #ifndef SRT_POOL_SPARE
 #define SRT_POOL_SPARE 2
 #endif
@@ -385,17 +386,19 @@ __device__ __noinline__ void fold_bundle(const KernelParams &P, uint32_t pix, ui
     float4 m = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                       // PreviousColor * (0/1), zeroed arena
     if (c != 0u || P.first_sample > 0u || !mean_mode) m = __ldcg(&P.accum[pix]);
 #pragma unroll 1
-    for (uint32_t j = 0; j < nvalid; ++j) {
-        const bool hi = j >= 32u;
-        const float ux = __shfl_sync(0xFFFFFFFFu, hi ? v1.x : v0.x, j & 31u);
-        const float uy = __shfl_sync(0xFFFFFFFFu, hi ? v1.y : v0.y, j & 31u);
-        const float uz = __shfl_sync(0xFFFFFFFFu, hi ? v1.z : v0.z, j & 31u);
-        if (mean_mode) {
-            const float wb = __shfl_sync(0xFFFFFFFFu, hi ? wb1 : wb0, j & 31u);
-            m.x = __fadd_rn(ux, __fmul_rn(wb, m.x)); m.y = __fadd_rn(uy, __fmul_rn(wb, m.y)); m.z = __fadd_rn(uz, __fmul_rn(wb, m.z));
-        } else {
-            m.x = __fadd_rn(m.x, ux); m.y = __fadd_rn(m.y, uy); m.z = __fadd_rn(m.z, uz);
+    for (uint32_t done = 0; done < nvalid; done += 32u) {                 // samples 0..31 from v0, then 32..63 from v1
+        const uint32_t cnt = min(32u, nvalid - done);
+#pragma unroll 1
+        for (uint32_t j = 0; j < cnt; ++j) {
+            const float ux = __shfl_sync(0xFFFFFFFFu, v0.x, j), uy = __shfl_sync(0xFFFFFFFFu, v0.y, j), uz = __shfl_sync(0xFFFFFFFFu, v0.z, j);
+            if (mean_mode) {
+                const float wb = __shfl_sync(0xFFFFFFFFu, wb0, j);
+                m.x = __fadd_rn(ux, __fmul_rn(wb, m.x)); m.y = __fadd_rn(uy, __fmul_rn(wb, m.y)); m.z = __fadd_rn(uz, __fmul_rn(wb, m.z));
+            } else {
+                m.x = __fadd_rn(m.x, ux); m.y = __fadd_rn(m.y, uy); m.z = __fadd_rn(m.z, uz);
+            }
         }
+        v0 = v1; wb0 = wb1;
     }
     if (c + 1u == P.n_chunks && mean_mode) {                              // A9, one channel per lane (one copy of the sqrt)
         const float v = lane == 0 ? m.x : (lane == 1 ? m.y : m.z);
@@ -424,7 +427,7 @@ render_pool(const __grid_constant__ KernelParams P) {
     float *const s_r2 = reinterpret_cast<float *>(s_slab + (n_res >> 2) * 3u);
     float *const st = s_r2 + n_res;
     uint32_t *const su = reinterpret_cast<uint32_t *>(st);
-    uint32_t *const ring0 = su + S_COUNT * NS;
+    uint32_t *const ring0 = su + (BUNDLE ? kBundleFields : S_COUNT) * NS;
     uint32_t *const ring1 = ring0 + RCAP;
     PoolCtl *const ctl = reinterpret_cast<PoolCtl *>(ring1 + RCAP);
     const uint32_t tid = threadIdx.x;
@@ -1004,9 +1007,9 @@ static render_kernel_t pick_pool_kernel_b(const srt_scene_options &o, bool strea
 static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream, int threads, bool bundle) {
     return bundle ? pick_pool_kernel_b<true>(o, stream, threads) : pick_pool_kernel_b<false>(o, stream, threads);
 }
-static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream) {
+static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream, bool bundle = false) {
     const size_t ns = 64u * (threads / 32 + kPoolSpareBatches), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
-    size_t bytes = (size_t)S_COUNT * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
+    size_t bytes = (size_t)(bundle ? kBundleFields : S_COUNT) * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
     if (stream) bytes += warps * kStreamStages * (kStreamStageF4 * sizeof(float4) + sizeof(uint64_t));
     else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
     return bytes;
@@ -1438,7 +1441,7 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     }
     render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, use_bundle) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
     const int threads = pool ? pool_threads : pairs ? pc.threads : kBlockThreads;
-    const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
+    const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream, use_bundle) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
     SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (pool) {   // leave the rest of the 256 KB to L1: the candidate queues live in local memory
         const size_t ctas = pool_threads == kPoolThreads && stream ? kPoolMinBlocks : 1;
