@@ -363,57 +363,33 @@ __device__ __forceinline__ void stream_bundle_pass(const float4 *__restrict__ sl
 }
 
 // Bundle mode, A8 (+ A9): all samples of chunk c of pixel `pix` are staged in row `row`; fold them into the
-// running mean in sample order (main.cpp:484-489 is sequential in k), publish the chunk count.  Called by
-// the whole warp with uniform arguments: lane l fetches samples l and l + 32 and their weights in parallel,
-// the recurrence itself is serial.
-__device__ __noinline__ void fold_bundle(const KernelParams &P, uint32_t pix, uint32_t row, uint32_t c, unsigned lane) {
-    __threadfence();                                                      // the other samples' staging stores
-    const uint32_t S = 1u << P.bundle_log2, n0 = c << P.bundle_log2;
-    const uint32_t nvalid = min(S, P.n_samples - n0);
+// running mean in sample order (main.cpp:484-489 is sequential in k) and publish the chunk count.  One chunk per
+// LANE: the slots that delivered a chunk's last sample queue up in ring F and a warp folds 32-64 chunks at a time
+// (folding each chunk by a whole warp as soon as it completed cost 8 % of the kernel's instructions).
+__device__ __forceinline__ void fold_chunk(const KernelParams &P, uint32_t pix, uint32_t row, uint32_t c) {
+    const uint32_t n0 = c << P.bundle_log2;
+    const uint32_t nvalid = min(1u << P.bundle_log2, P.n_samples - n0);
     const float4 *st = P.stage + ((size_t)row << P.bundle_log2);
-    float4 v0 = make_float4(0.f, 0.f, 0.f, 0.f), v1 = v0;
-    float wb0 = 0.0f, wb1 = 0.0f;
-    if (lane < nvalid) v0 = __ldcg(st + lane);
-    if (lane + 32u < nvalid) v1 = __ldcg(st + lane + 32u);
     const bool mean_mode = P.accum_mode == SRT_ACCUM_MEAN;
-    if (mean_mode) {                                                      // Out * (1/N), PrevCount/N with N = k + 1 (host table, IEEE)
-        const float2 w0 = lane < nvalid ? __ldg(P.fold_w + n0 + lane) : make_float2(0.f, 0.f);
-        const float2 w1 = lane + 32u < nvalid ? __ldg(P.fold_w + n0 + lane + 32u) : make_float2(0.f, 0.f);
-        wb0 = w0.y; wb1 = w1.y;
-        v0.x = __fmul_rn(w0.x, v0.x); v0.y = __fmul_rn(w0.x, v0.y); v0.z = __fmul_rn(w0.x, v0.z);
-        v1.x = __fmul_rn(w1.x, v1.x); v1.y = __fmul_rn(w1.x, v1.y); v1.z = __fmul_rn(w1.x, v1.z);
-    }
     float4 m = make_float4(0.0f, 0.0f, 0.0f, 0.0f);                       // PreviousColor * (0/1), zeroed arena
     if (c != 0u || P.first_sample > 0u || !mean_mode) m = __ldcg(&P.accum[pix]);
-#pragma unroll 1
-    for (uint32_t done = 0; done < nvalid; done += 32u) {                 // samples 0..31 from v0, then 32..63 from v1
-        const uint32_t cnt = min(32u, nvalid - done);
-#pragma unroll 1
-        for (uint32_t j = 0; j < cnt; ++j) {
-            const float ux = __shfl_sync(0xFFFFFFFFu, v0.x, j), uy = __shfl_sync(0xFFFFFFFFu, v0.y, j), uz = __shfl_sync(0xFFFFFFFFu, v0.z, j);
-            if (mean_mode) {
-                const float wb = __shfl_sync(0xFFFFFFFFu, wb0, j);
-                m.x = __fadd_rn(ux, __fmul_rn(wb, m.x)); m.y = __fadd_rn(uy, __fmul_rn(wb, m.y)); m.z = __fadd_rn(uz, __fmul_rn(wb, m.z));
-            } else {
-                m.x = __fadd_rn(m.x, ux); m.y = __fadd_rn(m.y, uy); m.z = __fadd_rn(m.z, uz);
-            }
+#pragma unroll 4
+    for (uint32_t j = 0; j < nvalid; ++j) {
+        const float4 v = __ldcg(st + j);
+        if (mean_mode) {                                                  // Out * (1/N) + Prev * (PrevCount/N), N = k + 1 (host table, IEEE)
+            const float2 w = __ldg(P.fold_w + n0 + j);
+            m.x = __fadd_rn(__fmul_rn(w.x, v.x), __fmul_rn(w.y, m.x));
+            m.y = __fadd_rn(__fmul_rn(w.x, v.y), __fmul_rn(w.y, m.y));
+            m.z = __fadd_rn(__fmul_rn(w.x, v.z), __fmul_rn(w.y, m.z));
+        } else {
+            m.x = __fadd_rn(m.x, v.x); m.y = __fadd_rn(m.y, v.y); m.z = __fadd_rn(m.z, v.z);
         }
-        v0 = v1; wb0 = wb1;
     }
-    if (c + 1u == P.n_chunks && mean_mode) {                              // A9, one channel per lane (one copy of the sqrt)
-        const float v = lane == 0 ? m.x : (lane == 1 ? m.y : m.z);
-        uint32_t q = to_u8(linear_to_srgb(v)) << (8u * (lane & 3u));
-        q |= __shfl_down_sync(0xFFFFFFFFu, q, 1);
-        q |= __shfl_down_sync(0xFFFFFFFFu, q, 2);
-        if (lane == 0) P.rgba[pix] = (q & 0x00FFFFFFu) | (255u << 24);
-    }
-    if (lane == 0) {
-        P.accum[pix] = make_float4(m.x, m.y, m.z, 1.0f);
-        P.cnt[row] = 0u;
-        __threadfence();                                                  // accum, cnt before the chunk count
-        *(volatile uint32_t *)&P.done[pix] = P.done_tag | (c + 1u);
-    }
-    __syncwarp();
+    P.accum[pix] = make_float4(m.x, m.y, m.z, 1.0f);
+    if (c + 1u == P.n_chunks && mean_mode) P.rgba[pix] = pack_rgba8(m.x, m.y, m.z);
+    P.cnt[row] = 0u;
+    __threadfence();                                                      // accum, cnt before the chunk count
+    *(volatile uint32_t *)&P.done[pix] = P.done_tag | (c + 1u);
 }
 
 template <int W, bool FMA, int THREADS, int MINB, bool STREAM, bool BUNDLE = false>
@@ -429,7 +405,8 @@ render_pool(const __grid_constant__ KernelParams P) {
     uint32_t *const su = reinterpret_cast<uint32_t *>(st);
     uint32_t *const ring0 = su + (BUNDLE ? kBundleFields : S_COUNT) * NS;
     uint32_t *const ring1 = ring0 + RCAP;
-    PoolCtl *const ctl = reinterpret_cast<PoolCtl *>(ring1 + RCAP);
+    uint32_t *const ring2 = ring1 + RCAP;                       // bundle mode only
+    PoolCtl *const ctl = reinterpret_cast<PoolCtl *>(ring2 + (BUNDLE ? RCAP : 0u));
     const uint32_t tid = threadIdx.x;
     const unsigned lane = tid & 31u;
     // streamed: per-warp TMA stages + barriers behind the control block (16-byte aligned)
@@ -463,10 +440,11 @@ render_pool(const __grid_constant__ KernelParams P) {
             SRT_SU(S_KEND, i) = k_end;
             SRT_SU(S_FLAGS, i) = 0u;
         }
-        for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? i : kRingEmpty; ring1[i] = kRingEmpty; }
+        for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? i : kRingEmpty; ring1[i] = kRingEmpty; if (BUNDLE) ring2[i] = kRingEmpty; }
         if (tid == 0) {
             ctl->head[0] = 0; ctl->tail[0] = NS; ctl->avail[0] = NS;
             ctl->head[1] = 0; ctl->tail[1] = 0; ctl->avail[1] = 0;
+            ctl->head[2] = 0; ctl->tail[2] = 0; ctl->avail[2] = 0;
             ctl->inflight = 0; ctl->retired = 0; ctl->spins_steady = 0; ctl->spins_tail = 0;
         }
     }
@@ -476,16 +454,30 @@ render_pool(const __grid_constant__ KernelParams P) {
 
     for (;;) {
         uint32_t kind = 0, n = 0, pos = 0;
-        if (lane == 0) pool_acquire(ctl, NS, hungry, kind, n, pos);
+        if (lane == 0) pool_acquire<BUNDLE>(ctl, NS, hungry, kind, n, pos);
         kind = __shfl_sync(0xFFFFFFFFu, kind, 0);
         n = __shfl_sync(0xFFFFFFFFu, n, 0);
         pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
         if (n == 0) break;
-        uint32_t *const ring = kind ? ring1 : ring0;
+        uint32_t *const ring = kind == 2u ? ring2 : (kind ? ring1 : ring0);
         uint32_t id0 = lane < n ? pool_pop(ring, RCAP - 1u, pos + lane) : kRingEmpty;
         uint32_t id1 = lane + 32u < n ? pool_pop(ring, RCAP - 1u, pos + 32u + lane) : kRingEmpty;
         __threadfence_block();
 
+        if (BUNDLE && kind == 2u) {
+            // ---- up to 64 slots that delivered the last sample of a pixel chunk: fold the chunks, one per lane (A8, A9) ----
+            __threadfence();                                              // the other samples' staging stores
+#pragma unroll 1
+            for (int r = 0; r < 2; ++r) {
+                const uint32_t s = r ? id1 : id0;
+                if (s != kRingEmpty) fold_chunk(P, SRT_SU(S_PIX, s), SRT_SU(S_PXY, s), SRT_SU(S_K, s) >> P.bundle_log2);
+                __syncwarp();
+                pool_push(ctl, ring0, RCAP - 1u, 0, s != kRingEmpty, s, lane);
+            }
+            hungry = false;
+            if (lane == 0) atomicSub(&ctl->inflight, 1u);
+            continue;
+        }
         f3 o0, o1, d0, d1;
         Hit h0, h1;
         Best b0 = best_init(), b1 = best_init();
@@ -747,16 +739,8 @@ render_pool(const __grid_constant__ KernelParams P) {
                     SRT_SU(S_FLAGS, s) = bounce;
                 }
             }
-            if (BUNDLE) {
-                unsigned fm = __ballot_sync(0xFFFFFFFFu, folds);
-                while (fm) {
-                    const int src = __ffs(fm) - 1;
-                    fm &= fm - 1u;
-                    const uint32_t fs = __shfl_sync(0xFFFFFFFFu, s, src);
-                    fold_bundle(P, SRT_SU(S_PIX, fs), SRT_SU(S_PXY, fs), SRT_SU(S_K, fs) >> P.bundle_log2, lane);
-                }
-            }
-            pool_push(ctl, ring0, RCAP - 1u, 0, (valid && ended) || waits, s, lane);
+            if (BUNDLE) pool_push(ctl, ring2, RCAP - 1u, 2, folds, s, lane);
+            pool_push(ctl, ring0, RCAP - 1u, 0, (valid && ended && !folds) || waits, s, lane);
             pool_push(ctl, ring1, RCAP - 1u, 1, valid && !ended, s, lane);
         }
         if (lane == 0) atomicSub(&ctl->inflight, 1u);
@@ -922,7 +906,8 @@ struct srt_backend {
     int slab_axis = 1;                   // axis contained in the slab planes: least spread of the centres
     double omax_scene = 0.0;             // >= |C| + r of every sphere (bound on secondary-ray origins)
     uint32_t pool_chunk = 0;             // samples per work item, 0 = kPoolChunkSamples (SRT_POOL_CHUNK)
-    int bundle = 1;                      // bundle mode of the pool kernel for launches of >= kBundleMinSamples samples (SRT_BUNDLE=0: off)
+    int bundle = 1;                      // bundle mode of the pool kernel: 1 = auto (>= kBundleMinSamples samples, >= kBundleMinSpheres
+                                         // spheres), 0 = off, k >= 2 = forced with chunks of <= 2^k samples (SRT_BUNDLE)
     float4 *d_stage = nullptr;           // bundle mode: staging rows of the pixels in flight (KernelParams::stage)
     uint32_t *d_cnt = nullptr;           // bundle mode: samples staged per row
     size_t stage_bytes = 0, cnt_rows = 0;
@@ -1009,7 +994,7 @@ static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream,
 }
 static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream, bool bundle = false) {
     const size_t ns = 64u * (threads / 32 + kPoolSpareBatches), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
-    size_t bytes = (size_t)(bundle ? kBundleFields : S_COUNT) * ns * sizeof(float) + 2 * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
+    size_t bytes = (size_t)(bundle ? kBundleFields : S_COUNT) * ns * sizeof(float) + (bundle ? 3 : 2) * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
     if (stream) bytes += warps * kStreamStages * (kStreamStageF4 * sizeof(float4) + sizeof(uint64_t));
     else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
     return bytes;
@@ -1020,6 +1005,7 @@ static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
 
 // Bundle mode (srt_bundle.cuh).
 constexpr uint32_t kBundleMinSamples = 8;        // launches with fewer samples keep (chunk, pixel) work items
+constexpr uint32_t kBundleMinSpheres = 768;     // smaller scenes keep them too (measured crossover between 482 and 1,024 spheres)
 constexpr uint32_t kBundleBandItemsLog2 = 21;
 static MagicDiv make_magic(uint32_t d) {          // srt_device.cuh: x / d for x < 2^30
     uint32_t l = 0;
@@ -1367,7 +1353,10 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         // are consecutive items; needs a sane pinhole camera (the footprint bound below) and 32-bit item indices
         bool bundle = false;
         uint32_t blog = 0;
-        if (b->bundle && args->n_samples >= kBundleMinSamples && !b->pool_chunk) {
+        // auto: scenes of >= kBundleMinSpheres (below that the per-ray scan is too short for the saving to pay for the
+        // staging and the larger code: 482 spheres -4 %, 1,024 +15 %, 65,536 +35 %); SRT_BUNDLE=0 off, =k >= 2 forces it
+        const bool want_bundle = b->bundle > 1 || (b->bundle == 1 && b->n_pad >= kBundleMinSpheres);
+        if (want_bundle && args->n_samples >= (b->bundle > 1 ? 4u : kBundleMinSamples) && !b->pool_chunk) {
             while (blog < 6u && (2u << blog) <= args->n_samples) ++blog;                 // S = min(64, 2^floor(log2 n))
             if (b->bundle > 1) blog = std::min<uint32_t>(blog, (uint32_t)b->bundle);     // SRT_BUNDLE=k (k >= 2): S <= 2^k (tests)
             const uint64_t S = 1ull << blog, n_chunks = (args->n_samples + S - 1) / S;

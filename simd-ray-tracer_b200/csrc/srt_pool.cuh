@@ -30,7 +30,8 @@ namespace srt {
 constexpr uint32_t kRingEmpty = 0xFFFFFFFFu;
 
 struct PoolCtl {
-    unsigned int head[2], tail[2], avail[2];   // ring 0 = P (needs a primary ray), ring 1 = S (secondary ready)
+    unsigned int head[3], tail[3], avail[3];   // ring 0 = P (needs a primary ray), ring 1 = S (secondary ready),
+                                               // ring 2 = F (bundle mode: holds the last sample of a pixel chunk, must fold it)
     unsigned int inflight;                     // warps currently holding a batch
     unsigned int retired;                      // slots that ran out of work
     unsigned int spins_steady, spins_tail;     // diagnostics: acquire-loop iterations before / after work ran out
@@ -64,16 +65,20 @@ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want_min, uint32_t &n, uint32_t
 // Lane 0 decides; returns n == 0 when every slot of the CTA has retired.  `hungry`: the caller's
 // last batch held no runnable path (all its slots wait for another slot's sample chunk): it may
 // take a partial batch of secondary rays, so the paths being waited for always advance.
+template <bool FOLD = false>
 __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, bool hungry, uint32_t &kind, uint32_t &n, uint32_t &pos) {
     n = 0; kind = 0; pos = 0;
     if (hungry) {
         __nanosleep(200);
+        if (FOLD && pool_try_take(ctl, 2, 1u, n, pos)) { kind = 2; return; }   // the chunk being waited for may sit in ring F
         if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
     }
     for (;;) {
+        if (FOLD && pool_try_take(ctl, 2, 32u, n, pos)) { kind = 2; return; }  // >= 32 chunks to fold: one per lane
         if (pool_try_take(ctl, 0, 64u, n, pos)) { kind = 0; return; }
         if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }
         if (*(volatile unsigned int *)&ctl->inflight == 0u) {            // nobody will add to the rings: drain partial batches
+            if (FOLD && pool_try_take(ctl, 2, 1u, n, pos)) { kind = 2; return; }
             if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
             if (pool_try_take(ctl, 0, 1u, n, pos)) { kind = 0; return; }
             if (*(volatile unsigned int *)&ctl->retired == n_slots) return;

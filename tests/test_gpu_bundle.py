@@ -1,4 +1,5 @@
-"""GPU: bundle mode of the pool kernel (csrc/srt_bundle.cuh) -- launches of >= 8 samples hand out single
+"""GPU: bundle mode of the pool kernel (csrc/srt_bundle.cuh) -- launches of >= 8 samples on scenes of >= 768
+spheres (forced here with SRT_BUNDLE=k on smaller scenes the oracle finishes quickly) hand out single
 samples as work items, so that a primary warp pass holds the samples of one pixel, runs the level-1 slab
 test once per (pixel, sphere) for the whole bundle, and folds the finished samples into the running mean
 in sample order from staging rows.
@@ -50,8 +51,8 @@ def _run(srt, env, monkeypatch, spheres, sky, W, fma, cam, w, h, launches):
         b.close()
 
 
-@pytest.mark.parametrize("env", [{}, {"SRT_BUNDLE": "2"}, {"SRT_BUNDLE": "3", "SRT_BUNDLE_BAND_ROWS": "1"}, {"SRT_BUNDLE_BAND_ROWS": "2"}],
-                         ids=["default", "S4", "S8_band1row", "band2rows"])
+@pytest.mark.parametrize("env", [{"SRT_BUNDLE": "6"}, {"SRT_BUNDLE": "2"}, {"SRT_BUNDLE": "3", "SRT_BUNDLE_BAND_ROWS": "1"}, {"SRT_BUNDLE": "5", "SRT_BUNDLE_BAND_ROWS": "2"}],
+                         ids=["S64", "S4", "S8_band1row", "S32_band2rows"])
 @pytest.mark.parametrize("mode", [(8, 1), (4, 0), (1, 0)])
 def test_bundle_equals_oracle(srt, oracle, monkeypatch, env, mode):
     W, fma = mode
@@ -70,7 +71,7 @@ def test_bundle_on_equals_bundle_off(srt, monkeypatch, scene, variant, size):
     w, h, spp = size
     spheres, sky, hdr = srt.host_scene(scene)
     cam = srt.host_camera(scene, w, h, hdr)
-    on = _run(srt, {"SRT_KERNEL_VARIANT": variant}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
+    on = _run(srt, {"SRT_KERNEL_VARIANT": variant, "SRT_BUNDLE": "6"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
     off = _run(srt, {"SRT_KERNEL_VARIANT": variant, "SRT_BUNDLE": "0"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
     assert _same(off, on) == {}
     small = _run(srt, {"SRT_KERNEL_VARIANT": variant, "SRT_BUNDLE": "3", "SRT_BUNDLE_BAND_ROWS": "3"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
@@ -79,8 +80,9 @@ def test_bundle_on_equals_bundle_off(srt, monkeypatch, scene, variant, size):
 
 def test_bundle_sum_shards(srt, oracle, monkeypatch):
     """The multi-GPU path: rank g adds samples k = g (mod N) to a plain sum, in k order."""
-    for k in ("SRT_BUNDLE", "SRT_BUNDLE_BAND_ROWS", "SRT_KERNEL_VARIANT", "SRT_POOL_CHUNK"):
+    for k in ("SRT_BUNDLE_BAND_ROWS", "SRT_KERNEL_VARIANT", "SRT_POOL_CHUNK"):
         monkeypatch.delenv(k, raising=False)
+    monkeypatch.setenv("SRT_BUNDLE", "6")
     spheres, sky, hdr = srt.host_scene(2)
     w, h, n, shards = 40, 30, 36, 3
     cam = srt.host_camera(2, w, h, hdr)
@@ -121,7 +123,7 @@ def test_bundle_camera_along_every_axis(srt, oracle, monkeypatch, axis):
     for pos in ((0.3, 9.0, 0.2), (9.0, 0.4, 0.1), (0.2, 0.5, 9.0)):
         cam = _look_camera(srt, pos, (0.0, 0.3, 0.0), w, h)
         o = oracle.render(spheres, sky, 8, 1, cam, w, h, 0, spp)
-        g = _run(srt, {"SRT_SLAB_AXIS": axis}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
+        g = _run(srt, {"SRT_SLAB_AXIS": axis, "SRT_BUNDLE": "6"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
         assert _same(o, g) == {}, pos
     monkeypatch.delenv("SRT_SLAB_AXIS", raising=False)
 
