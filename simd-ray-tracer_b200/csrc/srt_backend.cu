@@ -1005,8 +1005,8 @@ static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
 
 // Bundle mode (srt_bundle.cuh).
 constexpr uint32_t kBundleMinSamples = 8;        // launches with fewer samples keep (chunk, pixel) work items
-constexpr uint32_t kBundleMinSpheres = 768;     // smaller scenes keep them too (measured crossover between 482 and 1,024 spheres)
-constexpr uint32_t kBundleBandItemsLog2 = 21;
+constexpr uint64_t kBundleStageBytes = 1ull << 30;   // staging rows of one band (16 B x samples per chunk x pixels of the band)
+constexpr uint32_t kBundleMinSpheres = 768;      // smaller scenes keep them too (measured crossover between 482 and 1,024 spheres)
 static MagicDiv make_magic(uint32_t d) {          // srt_device.cuh: x / d for x < 2^30
     uint32_t l = 0;
     while ((1ull << l) < d) ++l;
@@ -1365,9 +1365,12 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
                 bundle = true;
                 P.bundle_log2 = blog;
                 P.n_chunks = (uint32_t)n_chunks;
-                // bands of whole block rows, ~2^21 work items per band and chunk (SRT_BUNDLE_BAND_ROWS: tests, tiny bands)
+                // bands of whole block rows, as large as kBundleStageBytes of staging rows allow (SRT_BUNDLE_BAND_ROWS: tests,
+                // tiny bands).  Measured: larger bands are faster (4K / 256 spp: 2 block rows 6,353, 64 rows 6,525 Mrays/s;
+                // 65,536 spheres: 17 rows 155, whole image 190) -- a chunk's fold waits in ring F for 31 others, and the next
+                // chunk / band of the same staging row must not start before it; L2 residency of the rows does not matter.
                 const uint32_t row_items = P.blocks_x * 32u, blocks_y = P.items_per_gen / row_items;
-                uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)(((1ull << kBundleBandItemsLog2) >> blog) / row_items));
+                uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)((kBundleStageBytes / (S * sizeof(float4))) / row_items));
                 if (const char *v = getenv("SRT_BUNDLE_BAND_ROWS")) band_rows = (uint32_t)std::max(1, atoi(v));
                 band_rows = std::min(band_rows, blocks_y);
                 P.n_bands = (blocks_y + band_rows - 1) / band_rows;
@@ -1383,7 +1386,11 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
                 if (need > b->stage_bytes || rows > b->cnt_rows) {
                     cudaFree(b->d_stage); cudaFree(b->d_cnt);
                     b->d_stage = nullptr; b->d_cnt = nullptr; b->stage_bytes = 0; b->cnt_rows = 0;
-                    SRT_CUDA(b, cudaMalloc(&b->d_stage, need));
+                    if (cudaMalloc(&b->d_stage, need) != cudaSuccess) {                   // not enough free memory for this band
+                        cudaGetLastError();
+                        b->d_stage = nullptr;
+                        return fail(b, SRT_ERR_CUDA, "srt_render: cannot allocate the bundle staging rows (set SRT_BUNDLE=0 or SRT_BUNDLE_BAND_ROWS)");
+                    }
                     SRT_CUDA(b, cudaMalloc(&b->d_cnt, rows * sizeof(uint32_t)));
                     b->stage_bytes = need;
                     b->cnt_rows = rows;
