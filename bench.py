@@ -316,22 +316,31 @@ def run_gpu_arm(args):
     pair_kernel = n_pad >= 64
     primary_per_launch = float(W * H * SPP) / max(1, n_gpus)   # one render launch per step per rank
     issue_cycles_per_sphere_pass = (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 64) / (rays_per_launch * n_pad / (kms * 1e-3))
+    # bundle mode (csrc/srt_bundle.cuh; auto from 768 spheres and 8 samples per launch): the primary passes run the
+    # level-1 test once per (pixel, sphere) for all samples of the pixel, 1/32 of the spheres per lane
+    bundle = pair_kernel and n_pad >= 768 and SPP // max(1, n_gpus) >= 8 and os.environ.get("SRT_BUNDLE", "1") != "0"
+    f_prim = min(1.0, primary_per_launch / max(1.0, rays_per_launch))
+    floor_pass = (8.06 * (1.0 - f_prim) + 0.35 * f_prim) if bundle else (8.06 if pair_kernel else 30.0)
+    exec_flop = (4.0 * (1.0 - f_prim) + 6.0 / 64.0 * f_prim) if bundle else (4.0 if pair_kernel else 20.0)
     roofline = {
         "bound": "fp32",
         "kernel": ("render_pool<8,true> (CTA-owned path slots, warp passes of 64 rays, two rays per thread: level-1 slab test of every "
-                   "sphere (2 FFMA2 + 2 FSETP per sphere per ray pair), level-2 fused 7-FMA filter on the survivors, the reference's "
-                   "arithmetic on what is left"
+                   "sphere (2 FFMA2 + 2 FSETP per sphere per ray pair"
+                   + ("; bundle mode: a primary pass holds the samples of one pixel and runs the test once per (pixel, sphere), "
+                      "1/32 of the spheres per lane" if bundle else "")
+                   + "), level-2 fused 7-FMA filter on the survivors, the reference's arithmetic on what is left"
                    + ("; tables streamed through per-warp TMA stages)" if n_pad > 8192 else "; tables resident in shared memory)")
                    if pair_kernel else "render_paths<8,true,true> (packed FFMA2 intersection loop)"),
         "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
         "peak_source": f"{info0['sm_count']} SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); "
                        "no tensor-core or HBM roof applies: the loop has no dense contraction and its scene is shared-memory resident",
         "algorithmic_flop_per_test": FLOP_PER_TEST, "tests_per_launch": rays_per_launch * n_pad,
-        "executed_flop_per_test": 4 if pair_kernel else 20,
-        "frac_executed": (4.0 if pair_kernel else 20.0) * rays_per_launch * n_pad / (kms * 1e-3) / 1e12 / peak_tflops,
+        "executed_flop_per_test": exec_flop,
+        "frac_executed": exec_flop * rays_per_launch * n_pad / (kms * 1e-3) / 1e12 / peak_tflops,
+        "bundle_mode": bool(bundle), "primary_ray_fraction": f_prim,
         "issue_cycles_per_sphere_per_warp_pass": issue_cycles_per_sphere_pass,
-        "issue_floor_cycles_per_sphere_per_warp_pass": 8.06 if pair_kernel else 30.0,
-        "issue_slot_frac": (8.06 if pair_kernel else 30.0) / issue_cycles_per_sphere_pass,
+        "issue_floor_cycles_per_sphere_per_warp_pass": floor_pass,
+        "issue_slot_frac": floor_pass / issue_cycles_per_sphere_pass,
         "issue_bound_note": ("`achieved`/`frac` count the reference's 20 flop per ray-sphere test (SURVEY 8d) and exceed the FP32 peak "
                              "because the kernel does not execute them: every sphere is tested against every ray with a conservative "
                              "2-FMA slab test (4 executed flop), ~2 % go on to a 7-FMA filter, ~0.2 % to the reference's 20-flop "
@@ -340,6 +349,8 @@ def run_gpu_arm(args):
                              "FSETP / LOP3 are not issued in its shadow (scripts/microbench/issue_mix.cu), so the level-1 floor is "
                              "2x2 + 2 + 1 + 0.75 + loop = 8.06 issue cycles per sphere per 64 rays; `issue_slot_frac` = that floor / "
                              "the measured whole-kernel cycles per sphere per 64 rays (regenerate, level 2, select, shade included)"
+                             + ("; in bundle mode the primary passes' share of the floor is 0.35 cycles per sphere (one 6-flop test per "
+                                "(pixel, sphere) for the 64 samples of the pass, DESIGN.md 5.2d), weighted by primary_ray_fraction" if bundle else "")
                              if pair_kernel else
                              "15 of the 20 flops' instructions are mandatory separate roundings (parity), so 15 FP32 issue cycles/test "
                              "is the hard floor: frac <= 20/30 = 0.667; see DESIGN.md"),
