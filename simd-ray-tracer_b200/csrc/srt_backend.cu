@@ -938,20 +938,25 @@ static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed, int 
     if (variant >= 2 && o.lane_width == 8 && o.fma_dot) {     // tuning experiments (W=8, FMA only)
         switch (variant) {
             case 2: return render_paths<8, true, true, 4, 3>;
-            case 3: return render_paths<8, true, true, 2, 3>;
-            case 4: return render_paths<8, true, true, 2, 4>;
             case 5: return render_paths<8, true, true, 4, 4>;
-            case 6: return render_paths<8, true, true, 1, 4>;
+            case 6: return render_paths<8, true, false, 4, 5>;
             default: break;
         }
     }
-    if (o.lane_width == 1) return render_paths<1, false, false>;
-    if (packed) {
-        if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, true> : render_paths<4, false, true>;
-        return o.fma_dot ? render_paths<8, true, true> : render_paths<8, false, true>;
+    // Tiny scenes are shading- and latency-bound: more resident warps beat the 104-register configuration (2 CTAs per SM).
+    // Demo scene, 1080p: scalar-issue loop at 4 CTAs / SM 32.7 Grays/s at 64 spp and 0.139 ms at 1 spp; packed loop at
+    // 3 CTAs / SM 31.4 and 0.147; before 27.3 and 0.193.  (A packed body must cover whole SIMD groups: 2 * PAIRS % W == 0.)
+    if (variant == 13) {                                       // the previous configuration, for A/B runs
+        if (o.lane_width == 1) return render_paths<1, false, false>;
+        if (o.lane_width == 8 && o.fma_dot) return packed ? render_paths<8, true, true> : render_paths<8, true, false>;
     }
-    if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, false> : render_paths<4, false, false>;
-    return o.fma_dot ? render_paths<8, true, false> : render_paths<8, false, false>;
+    if (o.lane_width == 1) return render_paths<1, false, false, 4, 4>;
+    if (packed) {
+        if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, true, 2, 4> : render_paths<4, false, true, 2, 4>;
+        return o.fma_dot ? render_paths<8, true, true, 4, 3> : render_paths<8, false, true, 4, 3>;
+    }
+    if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, false, 4, 4> : render_paths<4, false, false, 4, 4>;
+    return o.fma_dot ? render_paths<8, true, false, 4, 4> : render_paths<8, false, false, 4, 4>;
 }
 
 // Ray-pair kernel (srt_pairs.cuh): used when the scene is large enough for the intersection
@@ -1257,6 +1262,7 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.spheres = b->d_spheres;
     P.scan_table = b->d_scan;
     P.regen_threshold = b->regen_threshold;
+    if (b->n_pad <= 16u && args->n_samples <= 2u && !getenv("SRT_REGEN_THRESHOLD")) P.regen_threshold = 16u;   // 1 spp / frame: 0.139 vs 0.158 ms
     P.neg_one = -1.0f;
     P.one = 1.0f;
     P.materials = b->d_materials;
@@ -1324,7 +1330,8 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     const bool stream = pool && (b->variant == 12 || !pool_res_fit);
     const bool pairs = !pool && b->variant == 8;
     if (pairs && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
-    const bool packed = !pool && !pairs && (b->variant != 1) && b->opt.lane_width != 1;
+    // <= 16 spheres (the demo scene): shading-bound, the scalar-issue loop at 4 CTAs per SM is the fastest valid configuration
+    const bool packed = !pool && !pairs && (b->variant != 1) && b->opt.lane_width != 1 && (b->n_pad > 16u || b->variant >= 2);
     if (!pool && !pairs && (size_t)b->n_pad * sizeof(float4) > b->max_smem_optin)
         return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the one-path kernel");
     if (packed) P.spheres = b->d_spheres2;

@@ -60,6 +60,7 @@ __device__ __forceinline__ pk2 pk_dot(pk2 ax, pk2 ay, pk2 az, pk2 bx, pk2 by, pk
 template <int W, bool FMA, int PAIRS>
 __device__ __forceinline__ Hit intersect_lanes_packed(const float4 *__restrict__ sph2, uint32_t n_pad, f3 o, f3 d,
                                                       float neg_one_f, float one_f) {
+    static_assert((2 * PAIRS) % W == 0, "a loop body must cover whole SIMD groups: the lane of sphere e is e % W");
     float min_t[W];
     uint32_t group[W];
     uint32_t inside_bits = 0;
