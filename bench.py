@@ -316,9 +316,9 @@ def run_gpu_arm(args):
     pair_kernel = n_pad >= 64
     primary_per_launch = float(W * H * SPP) / max(1, n_gpus)   # one render launch per step per rank
     issue_cycles_per_sphere_pass = (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 64) / (rays_per_launch * n_pad / (kms * 1e-3))
-    # bundle mode (csrc/srt_bundle.cuh; auto from 768 spheres and 8 samples per launch): the primary passes run the
+    # bundle mode (csrc/srt_bundle.cuh; auto from 384 spheres and 8 samples per launch): the primary passes run the
     # level-1 test once per (pixel, sphere) for all samples of the pixel, 1/32 of the spheres per lane
-    bundle = pair_kernel and n_pad >= 768 and SPP // max(1, n_gpus) >= 8 and os.environ.get("SRT_BUNDLE", "1") != "0"
+    bundle = pair_kernel and n_pad >= 384 and SPP // max(1, n_gpus) >= 8 and os.environ.get("SRT_BUNDLE", "1") != "0"
     f_prim = min(1.0, primary_per_launch / max(1.0, rays_per_launch))
     floor_pass = (8.06 * (1.0 - f_prim) + 0.35 * f_prim) if bundle else (8.06 if pair_kernel else 30.0)
     exec_flop = (4.0 * (1.0 - f_prim) + 6.0 / 64.0 * f_prim) if bundle else (4.0 if pair_kernel else 20.0)

@@ -1011,7 +1011,7 @@ static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
 // Bundle mode (srt_bundle.cuh).
 constexpr uint32_t kBundleMinSamples = 8;        // launches with fewer samples keep (chunk, pixel) work items
 constexpr uint64_t kBundleStageBytes = 1ull << 30;   // staging rows of one band (16 B x samples per chunk x pixels of the band)
-constexpr uint32_t kBundleMinSpheres = 768;      // smaller scenes keep them too (measured crossover between 482 and 1,024 spheres)
+constexpr uint32_t kBundleMinSpheres = 384;      // measured (1080p, 32 spp): 256 spheres +1 %, 482 +9 %, 1,024 +18 %, 65,536 +57 %
 static MagicDiv make_magic(uint32_t d) {          // srt_device.cuh: x / d for x < 2^30
     uint32_t l = 0;
     while ((1ull << l) < d) ++l;
@@ -1361,7 +1361,8 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         bool bundle = false;
         uint32_t blog = 0;
         // auto: scenes of >= kBundleMinSpheres (below that the per-ray scan is too short for the saving to pay for the
-        // staging and the larger code: 482 spheres -4 %, 1,024 +15 %, 65,536 +35 %); SRT_BUNDLE=0 off, =k >= 2 forces it
+        // staging and the larger code) and launches of >= kBundleMinSamples samples (8 spp +8 %, 4 spp -2 %);
+        // SRT_BUNDLE=0 off, =k >= 2 forces it
         const bool want_bundle = b->bundle > 1 || (b->bundle == 1 && b->n_pad >= kBundleMinSpheres);
         if (want_bundle && args->n_samples >= (b->bundle > 1 ? 4u : kBundleMinSamples) && !b->pool_chunk) {
             while (blog < 6u && (2u << blog) <= args->n_samples) ++blog;                 // S = min(64, 2^floor(log2 n))

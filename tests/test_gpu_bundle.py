@@ -1,4 +1,4 @@
-"""GPU: bundle mode of the pool kernel (csrc/srt_bundle.cuh) -- launches of >= 8 samples on scenes of >= 768
+"""GPU: bundle mode of the pool kernel (csrc/srt_bundle.cuh) -- launches of >= 8 samples on scenes of >= 384
 spheres (forced here with SRT_BUNDLE=k on smaller scenes the oracle finishes quickly) hand out single
 samples as work items, so that a primary warp pass holds the samples of one pixel, runs the level-1 slab
 test once per (pixel, sphere) for the whole bundle, and folds the finished samples into the running mean
