@@ -105,3 +105,27 @@ def test_checkpoint_round_trip_and_rejects_damage(srt, tmp_path):
         bad.write_bytes(damaged)
         with pytest.raises(srt.SrtError):
             srt.load_checkpoint(bad)
+
+
+def test_magic_division_is_exact():
+    """Work-item decode of the pool kernel (csrc/srt_device.cuh magic_div, host side make_magic in srt_backend.cu):
+    x // d == (x * m) >> (30 + l) with m = ceil(2^(30+l) / d), 2^l >= d, for every x < 2^30.  Checked here on the
+    arithmetic itself (uint64 numpy) for the divisors the launches use (blocks per row, band sizes, band x chunks)
+    and random ones, at the multiples of d, their neighbours and random x."""
+    rng = np.random.default_rng(11)
+    ds = set(range(1, 700)) | {480 * 32 * 2, 480 * 32 * 68 * 4, 240 * 32 * 270, 15360, 30720, 983040, (1 << 26) - 1, 1 << 26}
+    ds |= set(int(v) for v in rng.integers(1, 1 << 27, 300))
+    for d in sorted(ds):
+        l = 0
+        while (1 << l) < d:
+            l += 1
+        m = ((1 << (30 + l)) + d - 1) // d
+        assert m < (1 << 32), d
+        kmax = ((1 << 30) - 1) // d
+        ks = np.unique(np.clip(np.concatenate([rng.integers(0, kmax + 1, 200), [0, 1, kmax]]), 0, kmax)).astype(np.uint64)
+        xs = np.concatenate([ks * np.uint64(d), ks * np.uint64(d) + np.uint64(d - 1), np.maximum(ks * np.uint64(d), np.uint64(1)) - np.uint64(1),
+                             rng.integers(0, 1 << 30, 400).astype(np.uint64), [np.uint64((1 << 30) - 1)]])
+        xs = xs[xs < np.uint64(1 << 30)]
+        # (x * m) < 2^62 fits uint64
+        q = (xs * np.uint64(m)) >> np.uint64(30 + l)
+        assert np.array_equal(q, xs // np.uint64(d)), d
