@@ -65,6 +65,11 @@ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want_min, uint32_t &n, uint32_t
 // Lane 0 decides; returns n == 0 when every slot of the CTA has retired.  `hungry`: the caller's
 // last batch held no runnable path (all its slots wait for another slot's sample chunk): it may
 // take a partial batch of secondary rays, so the paths being waited for always advance.
+#ifndef SRT_FOLD_MIN
+#define SRT_FOLD_MIN 64
+#endif
+constexpr uint32_t kFoldBatchMin = SRT_FOLD_MIN;   // ring F entries that make a fold pass worth a warp's while (two chunks per lane; 64 beats 32 and 16 by 1 %)
+
 template <bool FOLD = false>
 __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, bool hungry, uint32_t &kind, uint32_t &n, uint32_t &pos) {
     n = 0; kind = 0; pos = 0;
@@ -74,7 +79,7 @@ __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, boo
         if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
     }
     for (;;) {
-        if (FOLD && pool_try_take(ctl, 2, 32u, n, pos)) { kind = 2; return; }  // >= 32 chunks to fold: one per lane
+        if (FOLD && pool_try_take(ctl, 2, kFoldBatchMin, n, pos)) { kind = 2; return; }  // enough chunks to fold, one per lane
         if (pool_try_take(ctl, 0, 64u, n, pos)) { kind = 0; return; }
         if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }
         if (*(volatile unsigned int *)&ctl->inflight == 0u) {            // nobody will add to the rings: drain partial batches
