@@ -1375,7 +1375,7 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
                 P.n_chunks = (uint32_t)n_chunks;
                 // bands of whole block rows, as large as kBundleStageBytes of staging rows allow (SRT_BUNDLE_BAND_ROWS: tests,
                 // tiny bands).  Measured: larger bands are faster (4K / 256 spp: 2 block rows 6,353, 64 rows 6,525 Mrays/s;
-                // 65,536 spheres: 17 rows 155, whole image 190) -- a chunk's fold waits in ring F for 31 others, and the next
+                // 65,536 spheres: 17 rows 155, whole image 190) -- a chunk's fold waits in ring F for 63 others, and the next
                 // chunk / band of the same staging row must not start before it; L2 residency of the rows does not matter.
                 const uint32_t row_items = P.blocks_x * 32u, blocks_y = P.items_per_gen / row_items;
                 uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)((kBundleStageBytes / (S * sizeof(float4))) / row_items));
