@@ -1371,8 +1371,6 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
             const double rho = bundle_footprint(cam, b->width, b->height, P.slab_axis);
             if (rho > 0.0 && n_chunks <= 4095 && (uint64_t)P.items_per_gen * n_chunks * S < 0xF0000000ull) {
                 bundle = true;
-                P.bundle_log2 = blog;
-                P.n_chunks = (uint32_t)n_chunks;
                 // bands of whole block rows, as large as kBundleStageBytes of staging rows allow (SRT_BUNDLE_BAND_ROWS: tests,
                 // tiny bands).  Measured: larger bands are faster (4K / 256 spp: 2 block rows 6,353, 64 rows 6,525 Mrays/s;
                 // 65,536 spheres: 17 rows 155, whole image 190) -- a chunk's fold waits in ring F for 63 others, and the next
@@ -1381,6 +1379,28 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
                 uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)((kBundleStageBytes / (S * sizeof(float4))) / row_items));
                 if (const char *v = getenv("SRT_BUNDLE_BAND_ROWS")) band_rows = (uint32_t)std::max(1, atoi(v));
                 band_rows = std::min(band_rows, blocks_y);
+                size_t rows = 0, limit = ~(size_t)0;
+                if (const char *v = getenv("SRT_BUNDLE_STAGE_LIMIT")) limit = (size_t)atoll(v);   // tests: pretend larger allocations fail
+                for (;;) {                                                // smaller bands if the device is short of memory
+                    rows = (size_t)band_rows * row_items;
+                    const size_t need = rows * S * sizeof(float4);
+                    if (need <= b->stage_bytes && rows <= b->cnt_rows) break;
+                    cudaFree(b->d_stage); cudaFree(b->d_cnt);
+                    b->d_stage = nullptr; b->d_cnt = nullptr; b->stage_bytes = 0; b->cnt_rows = 0;
+                    if (need <= limit && cudaMalloc(&b->d_stage, need) == cudaSuccess && cudaMalloc(&b->d_cnt, rows * sizeof(uint32_t)) == cudaSuccess) {
+                        b->stage_bytes = need;
+                        b->cnt_rows = rows;
+                        break;
+                    }
+                    cudaGetLastError();
+                    cudaFree(b->d_stage); cudaFree(b->d_cnt);
+                    b->d_stage = nullptr; b->d_cnt = nullptr;
+                    if (band_rows == 1u) { bundle = false; break; }       // not even one block row: this launch runs without bundle mode
+                    band_rows = (band_rows + 1u) / 2u;
+                }
+                if (bundle) {
+                P.bundle_log2 = blog;
+                P.n_chunks = (uint32_t)n_chunks;
                 P.n_bands = (blocks_y + band_rows - 1) / band_rows;
                 P.band_items = band_rows * row_items;
                 P.band_last = P.items_per_gen - (P.n_bands - 1) * P.band_items;
@@ -1390,19 +1410,6 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
                 P.div_last = make_magic(P.band_last);
                 P.bundle_rho = (float)rho;
                 P.total_items = (uint32_t)((uint64_t)P.items_per_gen * n_chunks * S);
-                const size_t rows = P.band_items, need = rows * S * sizeof(float4);
-                if (need > b->stage_bytes || rows > b->cnt_rows) {
-                    cudaFree(b->d_stage); cudaFree(b->d_cnt);
-                    b->d_stage = nullptr; b->d_cnt = nullptr; b->stage_bytes = 0; b->cnt_rows = 0;
-                    if (cudaMalloc(&b->d_stage, need) != cudaSuccess) {                   // not enough free memory for this band
-                        cudaGetLastError();
-                        b->d_stage = nullptr;
-                        return fail(b, SRT_ERR_CUDA, "srt_render: cannot allocate the bundle staging rows (set SRT_BUNDLE=0 or SRT_BUNDLE_BAND_ROWS)");
-                    }
-                    SRT_CUDA(b, cudaMalloc(&b->d_cnt, rows * sizeof(uint32_t)));
-                    b->stage_bytes = need;
-                    b->cnt_rows = rows;
-                }
                 SRT_CUDA(b, cudaMemsetAsync(b->d_cnt, 0, rows * sizeof(uint32_t), b->stream));
                 P.stage = b->d_stage;
                 P.cnt = b->d_cnt;
@@ -1421,6 +1428,7 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
                     }
                     SRT_CUDA(b, cudaMemcpyAsync(b->d_fold_w, b->h_fold_w.data(), (size_t)args->n_samples * sizeof(float2), cudaMemcpyHostToDevice, b->stream));
                     P.fold_w = b->d_fold_w;
+                }
                 }
             }
         }

@@ -34,7 +34,7 @@ def _same(a, b, keys=("accum", "rgba", "prim", "t")):
 
 def _run(srt, env, monkeypatch, spheres, sky, W, fma, cam, w, h, launches):
     """launches: [(first, n)]; a fresh backend so that the SRT_* knobs are read."""
-    for k in ("SRT_BUNDLE", "SRT_BUNDLE_BAND_ROWS", "SRT_KERNEL_VARIANT", "SRT_POOL_CHUNK"):
+    for k in ("SRT_BUNDLE", "SRT_BUNDLE_BAND_ROWS", "SRT_BUNDLE_STAGE_LIMIT", "SRT_KERNEL_VARIANT", "SRT_POOL_CHUNK"):
         monkeypatch.delenv(k, raising=False)
     for k, v in env.items():
         monkeypatch.setenv(k, v)
@@ -76,6 +76,19 @@ def test_bundle_on_equals_bundle_off(srt, monkeypatch, scene, variant, size):
     assert _same(off, on) == {}
     small = _run(srt, {"SRT_KERNEL_VARIANT": variant, "SRT_BUNDLE": "3", "SRT_BUNDLE_BAND_ROWS": "3"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
     assert _same(off, small) == {}
+
+
+@pytest.mark.parametrize("limit", ["200000", "40000", "100"], ids=["half_bands", "one_block_row", "no_bundle"])
+def test_bundle_short_of_memory(srt, oracle, monkeypatch, limit):
+    """The staging rows do not fit (simulated with SRT_BUNDLE_STAGE_LIMIT): srt_render halves the band until they do
+    and, when not even one row of blocks fits, runs the launch without bundle mode.  Same bits every time."""
+    spheres, sky, hdr = srt.host_scene(2)
+    w, h, spp = 64, 36, 12
+    cam = srt.host_camera(2, w, h, hdr)
+    o = oracle.render(spheres, sky, 8, 1, cam, w, h, 0, spp)
+    g = _run(srt, {"SRT_BUNDLE": "6", "SRT_BUNDLE_STAGE_LIMIT": limit}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, spp)])
+    monkeypatch.delenv("SRT_BUNDLE_STAGE_LIMIT", raising=False)
+    assert _same(o, g) == {}
 
 
 def test_bundle_sum_shards(srt, oracle, monkeypatch):
