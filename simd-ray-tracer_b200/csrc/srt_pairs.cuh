@@ -344,52 +344,6 @@ __device__ __forceinline__ void scan_slab_tile(const float4 *__restrict__ tile, 
 // Every lane walks its own queue (flattened like select_update: the warp iterates
 // max-over-lanes(survivors) times), drops the bits the filter rejects and compacts the queue
 // (select_update relies on non-zero masks).
-#ifndef SRT_REFINE_PIPE
-#define SRT_REFINE_PIPE 0
-#endif
-#if SRT_REFINE_PIPE
-// Software-pipelined by one candidate: the sphere of candidate i+1 is fetched (queue entry from local memory,
-// gathered LDS.128) before the 7-FMA chain of candidate i is evaluated -- the loop is latency-bound (ncu: 26 % of
-// the warp-stall samples for 14 % of the instructions before this).
-template <class Fetch>
-__device__ __forceinline__ void refine_queue(const Fetch &fetch_scan, CandQueue &queue, uint32_t &qn, const ScanRays &r) {
-    uint32_t qi = 0, qo = 0, m = 0, first = 0, keep = 0;
-    uint32_t bit = 0, cfirst = 0;
-    bool last = false, have = false;
-    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-    // candidate 0
-    if (qn != 0u) {
-        const uint2 e = queue[qi++];                                         // masks in the queue are never 0
-        m = e.x; first = e.y;
-        const uint32_t j = (uint32_t)__clz((int)m);
-        bit = 0x80000000u >> j; m &= ~bit;
-        cfirst = first; last = m == 0u; s = fetch_scan(first + j); have = true;
-    }
-    while (have) {
-        // candidate i+1: index and sphere
-        uint32_t bit2 = 0, first2 = 0;
-        bool last2 = false, have2 = true;
-        float4 s2 = s;
-        if (m == 0u) {
-            if (qi == qn) have2 = false;
-            else { const uint2 e = queue[qi++]; m = e.x; first = e.y; }
-        }
-        if (have2) {
-            const uint32_t j = (uint32_t)__clz((int)m);
-            bit2 = 0x80000000u >> j; m &= ~bit2;
-            first2 = first; last2 = m == 0u; s2 = fetch_scan(first + j);
-        }
-        // candidate i
-        filter_sphere(keep, bit, s, r.p2ox, r.p2oy, r.p2oz, r.dx, r.dy, r.dz, r.od, r.ooa, r.oob);
-        if (last) {                                                          // compacted in place: qo <= entry of candidate i < qi
-            if (keep) { queue[qo] = make_uint2(keep, cfirst); qo += 1; }
-            keep = 0;
-        }
-        bit = bit2; cfirst = first2; last = last2; s = s2; have = have2;
-    }
-    qn = qo;
-}
-#else
 template <class Fetch>
 __device__ __forceinline__ void refine_queue(const Fetch &fetch_scan, CandQueue &queue, uint32_t &qn, const ScanRays &r) {
     // The queue lives in local memory and mostly misses the small L1 left beside 200 KB of shared memory (ncu: the
@@ -413,7 +367,6 @@ __device__ __forceinline__ void refine_queue(const Fetch &fetch_scan, CandQueue 
     }
     qn = qo;
 }
-#endif
 struct FetchScanResident { const float4 *scan; __device__ __forceinline__ float4 operator()(uint32_t idx) const { return scan[idx]; } };
 struct FetchScanGlobal { const float4 *scan; __device__ __forceinline__ float4 operator()(uint32_t idx) const { return __ldg(scan + idx); } };
 

@@ -37,16 +37,8 @@ struct PoolCtl {
     unsigned int spins_steady, spins_tail;     // diagnostics: acquire-loop iterations before / after work ran out
 };
 
-// Out of line: pool_acquire uses it seven times (instruction-cache footprint of the hot code).
-#ifndef SRT_TRYTAKE_NOINLINE
-#define SRT_TRYTAKE_NOINLINE 0
-#endif
-#if SRT_TRYTAKE_NOINLINE
-__device__ __noinline__
-#else
-__device__ __forceinline__
-#endif
-bool pool_try_take(PoolCtl *ctl, int q, uint32_t want_min, uint32_t &n, uint32_t &pos) {
+// Inline on purpose: an out-of-line copy (one instead of seven in pool_acquire) measured 6 % slower.
+__device__ __forceinline__ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want_min, uint32_t &n, uint32_t &pos) {
     unsigned int old = *(volatile unsigned int *)&ctl->avail[q];
     while (old >= want_min && old > 0u) {
         const unsigned int take = old < 64u ? old : 64u;
