@@ -403,9 +403,9 @@ render_pool(const __grid_constant__ KernelParams P) {
     float *const s_r2 = reinterpret_cast<float *>(s_slab + (n_res >> 2) * 3u);
     float *const st = s_r2 + n_res;
     uint32_t *const su = reinterpret_cast<uint32_t *>(st);
-    uint32_t *const ring0 = su + (BUNDLE ? kBundleFields : S_COUNT) * NS;
-    uint32_t *const ring1 = ring0 + RCAP;
-    uint32_t *const ring2 = ring1 + RCAP;                       // bundle mode only
+    ring_t *const ring0 = reinterpret_cast<ring_t *>(su + (BUNDLE ? kBundleFields : S_COUNT) * NS);
+    ring_t *const ring1 = ring0 + RCAP;
+    ring_t *const ring2 = ring1 + RCAP;                       // bundle mode only
     PoolCtl *const ctl = reinterpret_cast<PoolCtl *>(ring2 + (BUNDLE ? RCAP : 0u));
     const uint32_t tid = threadIdx.x;
     const unsigned lane = tid & 31u;
@@ -440,7 +440,7 @@ render_pool(const __grid_constant__ KernelParams P) {
             SRT_SU(S_KEND, i) = k_end;
             SRT_SU(S_FLAGS, i) = 0u;
         }
-        for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? i : kRingEmpty; ring1[i] = kRingEmpty; if (BUNDLE) ring2[i] = kRingEmpty; }
+        for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? (ring_t)i : kRingSlotEmpty; ring1[i] = kRingSlotEmpty; if (BUNDLE) ring2[i] = kRingSlotEmpty; }
         if (tid == 0) {
             ctl->head[0] = 0; ctl->tail[0] = NS; ctl->avail[0] = NS;
             ctl->head[1] = 0; ctl->tail[1] = 0; ctl->avail[1] = 0;
@@ -459,7 +459,7 @@ render_pool(const __grid_constant__ KernelParams P) {
         n = __shfl_sync(0xFFFFFFFFu, n, 0);
         pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
         if (n == 0) break;
-        uint32_t *const ring = kind == 2u ? ring2 : (kind ? ring1 : ring0);
+        ring_t *const ring = kind == 2u ? ring2 : (kind ? ring1 : ring0);
         uint32_t id0 = lane < n ? pool_pop(ring, RCAP - 1u, pos + lane) : kRingEmpty;
         uint32_t id1 = lane + 32u < n ? pool_pop(ring, RCAP - 1u, pos + 32u + lane) : kRingEmpty;
         __threadfence_block();
@@ -999,7 +999,7 @@ static render_kernel_t pick_pool_kernel(const srt_scene_options &o, bool stream,
 }
 static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream, bool bundle = false) {
     const size_t ns = 64u * (threads / 32 + kPoolSpareBatches), rcap = ns <= 1024 ? 1024 : 2048, warps = threads / 32;
-    size_t bytes = (size_t)(bundle ? kBundleFields : S_COUNT) * ns * sizeof(float) + (bundle ? 3 : 2) * rcap * sizeof(uint32_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
+    size_t bytes = (size_t)(bundle ? kBundleFields : S_COUNT) * ns * sizeof(float) + (bundle ? 3 : 2) * rcap * sizeof(ring_t) + ((sizeof(PoolCtl) + 15u) & ~(size_t)15u);
     if (stream) bytes += warps * kStreamStages * (kStreamStageF4 * sizeof(float4) + sizeof(uint64_t));
     else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
     return bytes;

@@ -27,7 +27,12 @@
 
 namespace srt {
 
-constexpr uint32_t kRingEmpty = 0xFFFFFFFFu;
+constexpr uint32_t kRingEmpty = 0xFFFFFFFFu;   // `no slot` in registers
+// Ring entries are 16-bit slot ids (< 2,048 slots per CTA): with three rings of 2,048 entries the bundle-mode CTA
+// stays under 196 KB of shared memory, the largest carve-out that leaves 60 KB (instead of 28 KB) of L1 for the
+// candidate queues in local memory.
+typedef uint16_t ring_t;
+constexpr ring_t kRingSlotEmpty = 0xFFFFu;
 
 struct PoolCtl {
     unsigned int head[3], tail[3], avail[3];   // ring 0 = P (needs a primary ray), ring 1 = S (secondary ready),
@@ -85,16 +90,16 @@ __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, boo
     }
 }
 
-__device__ __forceinline__ uint32_t pool_pop(uint32_t *ring, uint32_t cap_mask, uint32_t pos) {
-    volatile uint32_t *e = ring + (pos & cap_mask);
-    uint32_t id;
-    while ((id = *e) == kRingEmpty) { }
-    *e = kRingEmpty;
+__device__ __forceinline__ uint32_t pool_pop(ring_t *ring, uint32_t cap_mask, uint32_t pos) {
+    volatile ring_t *e = ring + (pos & cap_mask);
+    ring_t id;
+    while ((id = *e) == kRingSlotEmpty) { }
+    *e = kRingSlotEmpty;
     return id;
 }
 
 // Warp-aggregated push of `id` by the lanes with `doit`.
-__device__ __forceinline__ void pool_push(PoolCtl *ctl, uint32_t *ring, uint32_t cap_mask, int q, bool doit, uint32_t id, unsigned lane) {
+__device__ __forceinline__ void pool_push(PoolCtl *ctl, ring_t *ring, uint32_t cap_mask, int q, bool doit, uint32_t id, unsigned lane) {
     const unsigned m = __ballot_sync(0xFFFFFFFFu, doit);
     if (m == 0u) return;
     const unsigned leader = __ffs(m) - 1;
@@ -102,9 +107,9 @@ __device__ __forceinline__ void pool_push(PoolCtl *ctl, uint32_t *ring, uint32_t
     if (lane == leader) pos = atomicAdd(&ctl->tail[q], __popc(m));
     pos = __shfl_sync(0xFFFFFFFFu, pos, leader);
     if (doit) {
-        volatile uint32_t *e = ring + ((pos + __popc(m & ((1u << lane) - 1u))) & cap_mask);
-        while (*e != kRingEmpty) { }
-        *e = id;
+        volatile ring_t *e = ring + ((pos + __popc(m & ((1u << lane) - 1u))) & cap_mask);
+        while (*e != kRingSlotEmpty) { }
+        *e = (ring_t)id;
     }
     __threadfence_block();
     __syncwarp();
