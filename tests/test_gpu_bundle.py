@@ -161,3 +161,22 @@ def test_bundle_audit(backend, srt, scene):
         backend.set_scene(s2, sky, 8, True)
         a = backend.filter_audit(c2, 0, 2)
         assert a["bundle_violations"] == 0 and a["violations"] == 0, (off, a)
+
+
+def test_bundle_fuzz_against_non_bundle(srt, monkeypatch):
+    """Random image sizes, sample counts, resumed launches, chunk sizes and band sizes on the 1,024-sphere scene:
+    every buffer of a bundle-mode accumulation equals the non-bundle kernel's (which the other tests pin to the
+    oracle).  Exercises ragged block edges, short last bands, short last chunks and staging-row reuse together."""
+    rng = np.random.default_rng(20261105)
+    spheres, sky, hdr = srt.host_scene(3)
+    for case in range(24):
+        w, h = int(rng.integers(1, 150)), int(rng.integers(1, 90))
+        n1, n2 = int(rng.integers(8, 70)), int(rng.integers(0, 20))
+        launches = [(0, n1)] + ([(n1, n2)] if n2 else [])
+        env = {"SRT_BUNDLE": str(int(rng.integers(2, 7)))}
+        if rng.integers(0, 2):
+            env["SRT_BUNDLE_BAND_ROWS"] = str(int(rng.integers(1, 6)))
+        cam = srt.host_camera(3, w, h, hdr)
+        on = _run(srt, env, monkeypatch, spheres, sky, 8, 1, cam, w, h, launches)
+        off = _run(srt, {"SRT_BUNDLE": "0"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, launches)
+        assert _same(off, on) == {}, (case, w, h, launches, env)
