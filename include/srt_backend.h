@@ -11,6 +11,9 @@
  * SRT_OK (0) or a negative srt_status; srt_last_error() describes the last failure.
  * The library has NO CPU fallback: without a CUDA device srt_create fails.
  * One host thread per handle; at most one render in flight per handle.
+ * Several devices: one handle per device (srt_create(.., device_id)), one host thread or
+ * process each, joined by srt_comm_init_rank -- the counterpart of the ThreadCount argument of
+ * WorkQueueCreate / WorkQueueStart (base.h:172-174, main.cpp:660, 851-856).
  */
 #ifndef SRT_BACKEND_H
 #define SRT_BACKEND_H
@@ -24,7 +27,8 @@ typedef enum {
     SRT_ERR_INVALID = -1,     /* bad argument / call order */
     SRT_ERR_CUDA = -2,        /* CUDA runtime error (see srt_last_error) */
     SRT_ERR_NO_DEVICE = -3,   /* no usable sm_100 device */
-    SRT_ERR_TOO_LARGE = -4    /* scene / image exceeds a backend limit */
+    SRT_ERR_TOO_LARGE = -4,   /* scene / image exceeds a backend limit */
+    SRT_ERR_COMM = -5         /* NCCL missing or a collective failed (see srt_last_error) */
 } srt_status;
 
 /* POD mirror of `material`, main.cpp:11-16 (v3 is 16 bytes: x,y,z,_w; base.h:357-375). 48 B */
@@ -87,7 +91,8 @@ typedef struct srt_render_args {
 
 typedef struct srt_backend srt_backend;
 
-/* Lifetime. device_id: CUDA ordinal. */
+/* Lifetime. device_id: CUDA ordinal.  On failure *out is NULL (nothing to destroy) and
+ * srt_last_error(NULL) holds the reason. */
 int srt_create(srt_backend **out, int device_id);
 void srt_destroy(srt_backend *b);
 const char *srt_last_error(const srt_backend *b);   /* b may be NULL: last create error */
@@ -98,7 +103,7 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
                   const srt_scene_options *options);
 
 /* (Re)allocate PreviousImage (f32x4) + CurrentImage (RGBA8) on the device and reset the
- * accumulation, like main.cpp:797-804. */
+ * accumulation, like main.cpp:797-804.  width, height <= 65535 and width * height < 2^31. */
 int srt_resize(srt_backend *b, uint32_t width, uint32_t height);
 /* Reset only (camera moved / key R, main.cpp:791-798): zeroes the accumulator. */
 int srt_reset_accumulation(srt_backend *b);
@@ -137,7 +142,56 @@ int srt_read_primary(srt_backend *b, uint32_t *prim /* 0xFFFFFFFF = miss */, flo
  * resume an interrupted accumulation -- the next srt_render continues with
  * first_sample = the number of samples the buffer holds (checkpoint/resume; the reference keeps
  * PreviousImage only in its arena, main.cpp:801-804). */
-int srt_write_accum(srt_backend *b, const float *src /* W*H*4 floats */);
+int srt_write_accum(srt_backend *b, const float *src /* W*H*4 floats */);   /* a partitioned handle keeps its own rows only */
+
+/* ---- several devices (one handle each) -----------------------------------------------------
+ * The reference fans a frame out to ThreadCount worker threads that pull 32x32 tiles
+ * (WorkQueueStart base.h:174, main.cpp:851-856; tiles main.cpp:9, 362-368, 824-827).  Here the
+ * workers are GPUs.  Two partitions of a frame are supported:
+ *   image partition  srt_set_partition(part, n_parts): the handle renders every n_parts-th row of
+ *                    8x4-pixel blocks (rows part, part + n_parts, ...) with ALL samples and the exact
+ *                    running mean; rows of other devices stay zero, so srt_gather_rgba /
+ *                    srt_gather_accum (an NCCL sum) return an image that is BIT-IDENTICAL to a
+ *                    single-device render;
+ *   sample partition srt_render(first_sample = rank, sample_stride = n_ranks, SRT_ACCUM_SUM) on every
+ *                    device, srt_reduce_accum(root), srt_resolve_sum(total) on the root (sum-then-divide:
+ *                    within the stated tolerance of the running mean, not bit-identical).
+ * NCCL is loaded at run time (the libnccl.so.2 already in the process, else the loader's); the
+ * collectives run on the handle's stream, ordered after its renders.  Every rank must make the same
+ * sequence of srt_comm_init_rank / srt_reduce_accum / srt_gather_* calls. */
+#define SRT_COMM_ID_BYTES 128
+int srt_comm_unique_id(void *id_out /* SRT_COMM_ID_BYTES; made by one rank, given to all */);
+int srt_comm_init_rank(srt_backend *b, int n_ranks, int rank, const void *unique_id);   /* collective */
+int srt_comm_destroy(srt_backend *b);
+/* A host thread that drives SEVERAL handles brackets the init calls, and each round of srt_reduce_accum /
+ * srt_gather_* calls over its handles, with these (ncclGroupStart / ncclGroupEnd). */
+int srt_comm_group_begin(void);
+int srt_comm_group_end(void);
+int srt_comm_info(srt_backend *b, int *rank, int *n_ranks /* 0: no communicator */, int *nccl_version);
+/* Image partition of this handle; resets the accumulation when it changes. Default (0, 1): whole image. */
+int srt_set_partition(srt_backend *b, uint32_t part, uint32_t n_parts);
+/* In-place f32 sum of the accumulators onto `root` (root < 0: onto every rank). */
+int srt_reduce_accum(srt_backend *b, int root);
+/* Combine the row bands of an image partition on `root` (root < 0: on every rank).  Afterwards
+ * srt_read_rgba8 / srt_read_accum on a receiving rank return the combined image, until its next
+ * render or reset. */
+int srt_gather_rgba(srt_backend *b, int root);
+int srt_gather_accum(srt_backend *b, int root);
+
+/* Diagnostic: run the device functions the kernels are built from on caller-provided records (host
+ * buffers), n records, one per thread.  Record layouts (in -> out):
+ *   SRT_KAT_PCG            u64 state                      -> 16 x u32 draws        (base.h:954-963)
+ *   SRT_KAT_RANDOM_FLOAT   {u64 state, f32 InverseMaxInt, f32 Min} -> 16 x f32     (base.h:983-989)
+ *   SRT_KAT_STREAM_SEED    u64 index                      -> u64                    (main.cpp:667-676)
+ *   SRT_KAT_NORMALIZE      3 x f32                        -> 3 x f32                (x64_math.h:234-245)
+ *   SRT_KAT_REFLECTANCE    {f32 cos, f32 eta}             -> f32                    (main.cpp:292-300)
+ *   SRT_KAT_LINEAR_TO_SRGB f32                            -> f32                    (main.cpp:312-322)
+ *   SRT_KAT_PACK           4 x f32 {r, g, b, -} linear    -> u32 RGBA8              (main.cpp:324-346) */
+typedef enum {
+    SRT_KAT_PCG = 0, SRT_KAT_RANDOM_FLOAT, SRT_KAT_STREAM_SEED, SRT_KAT_NORMALIZE, SRT_KAT_REFLECTANCE,
+    SRT_KAT_LINEAR_TO_SRGB, SRT_KAT_PACK, SRT_KAT_COUNT
+} srt_kat_op;
+int srt_device_kat(srt_backend *b, uint32_t op, const void *in, uint32_t n, void *out);
 
 /* Device pointers / stream of the current buffers (for collectives and graphs). */
 void *srt_accum_device_ptr(srt_backend *b);

@@ -36,8 +36,17 @@ EXPORTS = [
     "srt_reset_accumulation", "srt_bind_device_buffers", "srt_render", "srt_poll", "srt_wait",
     "srt_resolve_sum", "srt_read_rgba8", "srt_read_accum", "srt_read_primary",
     "srt_accum_device_ptr", "srt_rgba_device_ptr", "srt_cuda_stream", "srt_device_info",
-    "srt_filter_audit", "srt_write_accum",
+    "srt_filter_audit", "srt_write_accum", "srt_device_kat",
+    "srt_comm_unique_id", "srt_comm_init_rank", "srt_comm_destroy", "srt_comm_info", "srt_set_partition",
+    "srt_reduce_accum", "srt_gather_rgba", "srt_gather_accum", "srt_comm_group_begin", "srt_comm_group_end",
 ]
+COMM_ID_BYTES = 128
+KAT_PCG, KAT_RANDOM_FLOAT, KAT_STREAM_SEED, KAT_NORMALIZE, KAT_REFLECTANCE, KAT_LINEAR_TO_SRGB, KAT_PACK = range(7)
+_KAT_IO = {  # op: (input dtype, values per record in, output dtype, values per record out)
+    KAT_PCG: (np.uint64, 1, np.uint32, 16), KAT_RANDOM_FLOAT: (np.uint64, 2, np.float32, 16),
+    KAT_STREAM_SEED: (np.uint64, 1, np.uint64, 1), KAT_NORMALIZE: (np.float32, 3, np.float32, 3),
+    KAT_REFLECTANCE: (np.float32, 2, np.float32, 1), KAT_LINEAR_TO_SRGB: (np.float32, 1, np.float32, 1),
+    KAT_PACK: (np.float32, 4, np.uint32, 1)}
 
 
 class SceneOptions(C.Structure):
@@ -58,13 +67,15 @@ _lib = None
 
 
 def load_library():
-    """dlopen libsrt_cuda.so (no compute). Raises if it has not been built."""
+    """dlopen libsrt_cuda.so (no compute). Raises if it has not been built.
+    SRT_CUDA_LIB selects another build of the same ABI (the -DSRT_SPIN_LIMIT debug library)."""
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
-        raise SrtError(f"{LIB_PATH} is missing: run __graft_entry__.build() (nvcc). There is no CPU fallback.")
-    L = C.CDLL(LIB_PATH)
+    path = os.environ.get("SRT_CUDA_LIB", LIB_PATH)
+    if not os.path.exists(path):
+        raise SrtError(f"{path} is missing: run __graft_entry__.build() (nvcc). There is no CPU fallback.")
+    L = C.CDLL(path)
     vp = C.c_void_p
     L.srt_create.argtypes = [C.POINTER(vp), C.c_int]
     L.srt_destroy.argtypes = [vp]
@@ -88,6 +99,15 @@ def load_library():
         getattr(L, f).argtypes = [vp]
         getattr(L, f).restype = vp
     L.srt_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
+    L.srt_device_kat.argtypes = [vp, C.c_uint32, vp, C.c_uint32, vp]
+    L.srt_comm_unique_id.argtypes = [vp]
+    L.srt_comm_init_rank.argtypes = [vp, C.c_int, C.c_int, vp]
+    L.srt_comm_destroy.argtypes = [vp]
+    L.srt_comm_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.srt_set_partition.argtypes = [vp, C.c_uint32, C.c_uint32]
+    L.srt_reduce_accum.argtypes = [vp, C.c_int]
+    L.srt_gather_rgba.argtypes = [vp, C.c_int]
+    L.srt_gather_accum.argtypes = [vp, C.c_int]
     _lib = L
     return L
 
@@ -185,6 +205,40 @@ class Backend:
         self._check(self.L.srt_read_primary(self.h, prim.ctypes.data, t.ctypes.data))
         return prim, t
 
+    def device_kat(self, op, records):
+        """Run device function `op` (KAT_*) on `records` (one row per record); returns one row of outputs per record."""
+        it, ni, ot, no = _KAT_IO[op]
+        a = np.ascontiguousarray(records, it).reshape(-1, ni)
+        out = np.zeros((len(a), no), ot)
+        self._check(self.L.srt_device_kat(self.h, op, a.ctypes.data, len(a), out.ctypes.data))
+        return out
+
+    # ---- several devices (one handle per device / process) --------------------------------
+    def comm_init_rank(self, n_ranks, rank, unique_id):
+        buf = np.frombuffer(bytes(unique_id), np.uint8).copy()
+        assert buf.nbytes == COMM_ID_BYTES
+        self._check(self.L.srt_comm_init_rank(self.h, n_ranks, rank, buf.ctypes.data))
+
+    def comm_destroy(self):
+        self._check(self.L.srt_comm_destroy(self.h))
+
+    def comm_info(self):
+        r, n, v = C.c_int(), C.c_int(), C.c_int()
+        self._check(self.L.srt_comm_info(self.h, C.byref(r), C.byref(n), C.byref(v)))
+        return dict(rank=r.value, n_ranks=n.value, nccl_version=v.value)
+
+    def set_partition(self, part, n_parts):
+        self._check(self.L.srt_set_partition(self.h, part, n_parts))
+
+    def reduce_accum(self, root=0):
+        self._check(self.L.srt_reduce_accum(self.h, root))
+
+    def gather_rgba(self, root=0):
+        self._check(self.L.srt_gather_rgba(self.h, root))
+
+    def gather_accum(self, root=0):
+        self._check(self.L.srt_gather_accum(self.h, root))
+
     def device_info(self):
         sm, khz, n = C.c_int(), C.c_int(), C.c_uint64()
         self._check(self.L.srt_device_info(self.h, C.byref(sm), C.byref(khz), C.byref(n)))
@@ -201,6 +255,16 @@ class Backend:
     @property
     def stream_ptr(self):
         return self.L.srt_cuda_stream(self.h)
+
+
+def comm_unique_id():
+    """128-byte NCCL unique id (made by one rank, handed to every rank's Backend.comm_init_rank)."""
+    L = load_library()
+    buf = np.zeros(COMM_ID_BYTES, np.uint8)
+    rc = L.srt_comm_unique_id(buf.ctypes.data)
+    if rc != 0:
+        raise SrtError(f"srt_comm_unique_id failed ({rc}): {L.srt_last_error(None).decode()}")
+    return buf.tobytes()
 
 
 # ---- host mirror (C++): scene tables and camera, no GPU needed ------------------------------
@@ -222,6 +286,8 @@ def load_host_library():
         H.srt_host_load_scene.argtypes = [C.c_uint, C.c_char_p]
         H.srt_host_reset_scene.argtypes = [C.c_uint]
         H.srt_host_reset_scene.restype = None
+        H.srt_host_scene_hash.argtypes = [C.c_uint]
+        H.srt_host_scene_hash.restype = C.c_ulonglong
         H.srt_host_save_checkpoint.argtypes = [C.c_char_p, C.c_void_p, C.c_ulonglong, C.c_void_p]
         H.srt_host_load_checkpoint.argtypes = [C.c_char_p, C.c_void_p, C.POINTER(C.c_ulonglong), C.c_void_p, C.c_ulonglong]
         _hostlib = H
@@ -243,6 +309,11 @@ def load_scene_file(index, path):
 def reset_scene(index):
     """Undo load_scene_file: slot `index` is rebuilt as the built-in / synthetic scene on next use."""
     load_host_library().srt_host_reset_scene(index)
+
+
+def host_scene_hash(index):
+    """FNV-1a of scene slot `index` (sphere records + sky flag): what a checkpoint pins its scene with."""
+    return int(load_host_library().srt_host_scene_hash(index))
 
 
 def save_checkpoint(path, accum, samples, scene_index, stream_base=0, lane_width=8, fma_dot=1):

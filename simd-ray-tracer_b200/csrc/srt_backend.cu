@@ -12,6 +12,7 @@
 #include "srt_pool.cuh"
 #include "srt_bundle.cuh"
 #include "srt_stream.cuh"
+#include "srt_comm.h"
 
 #include <algorithm>
 #include <cmath>
@@ -126,22 +127,10 @@ render_paths(const __grid_constant__ KernelParams P) {
         }
     }
 
-    // rays: one atomic per warp
-    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
-    if (lane == 0 && rays) atomicAdd(P.rays, rays);
+    finish_launch(P, rays);
 }
 
-// ------------------------------------------------------------------------------------------
-// render_pairs: the same pipeline A1..A9 with TWO paths per thread (slot 0 / slot 1) packed
-// into the halves of Blackwell's f32x2 instructions (srt_pairs.cuh: fused filter over all
-// spheres, reference arithmetic on the candidates).  Used when the intersection loop
-// dominates (>= kPairsMinSpheres spheres).
-//
-// Everything a path carries between bounces -- ray, attenuation, radiance, running mean, RNG
-// state, pixel, sample index -- is parked in shared memory (field-major, conflict-free), so
-// the registers of the hot loop hold nothing but the two packed rays and its temporaries, and
-// the regenerate / shade phases are plain run-time loops over the two slots.
-// ------------------------------------------------------------------------------------------
+// Path state of one slot of the pool kernel, parked in shared memory (field-major: conflict-free).
 enum : int { S_OX, S_OY, S_OZ, S_DX, S_DY, S_DZ, S_AX, S_AY, S_AZ, S_LX, S_LY, S_LZ,
              S_RNG_LO, S_RNG_HI, S_PIX, S_K, S_PXY, S_FLAGS, S_KEND, S_MX, S_MY, S_MZ, S_COUNT };
 constexpr int kBundleFields = S_COUNT - 3;   // bundle mode keeps no running mean in the slot (S_MX..S_MZ): 23 KB more L1 for the queues
@@ -149,151 +138,19 @@ constexpr int kBundleFields = S_COUNT - 3;   // bundle mode keeps no running mea
 #define SRT_POOL_SPARE 2
 #endif
 constexpr uint32_t kPoolSpareBatches = SRT_POOL_SPARE;   // path slots per CTA = 64 x (warps + spare)
-constexpr uint32_t kFlagBounceMask = 7u, kFlagActive = 8u, kFlagDone = 16u, kFlagPending = 32u;
-
-template <int W, bool FMA, int THREADS, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB)
-render_pairs(const __grid_constant__ KernelParams P) {
-    extern __shared__ float4 s_scan[];                     // {cx,cy,cz,-kappa}: centres + filter constant
-    float *const s_r2 = reinterpret_cast<float *>(s_scan + P.n_pad);
-    float *const st = s_r2 + P.n_pad;
-    uint32_t *const su = reinterpret_cast<uint32_t *>(st);
-    const uint32_t tid = threadIdx.x;
-    const unsigned lane = tid & 31u;
-#define SRT_ST(f, r) st[(((f) * THREADS) + tid) * 2 + (r)]
-#define SRT_SU(f, r) su[(((f) * THREADS) + tid) * 2 + (r)]
-    for (uint32_t i = tid; i < P.n_pad; i += THREADS) { s_scan[i] = P.scan_table[i]; s_r2[i] = P.spheres[i].w; }
-    const uint32_t k_end = P.first_sample + P.n_samples * P.sample_stride;
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-        SRT_SU(S_PIX, r) = kInvalidPixel;
-        SRT_SU(S_K, r) = k_end;
-        SRT_SU(S_FLAGS, r) = 0u;
-    }
-    __syncthreads();
-    unsigned long long rays = 0;
-
-    for (;;) {
-        // ---- regenerate: finish pixels, fetch new ones, start new paths ----------------------
-        bool all_done = true;
-#pragma unroll 1
-        for (int r = 0; r < 2; ++r) {
-            uint32_t flags = SRT_SU(S_FLAGS, r);
-            const bool idle = (flags & (kFlagActive | kFlagDone)) == 0u;
-            if (__any_sync(0xFFFFFFFFu, idle)) {
-                uint32_t pix = SRT_SU(S_PIX, r), k = SRT_SU(S_K, r), pxy = SRT_SU(S_PXY, r);
-                bool need = idle && (k == k_end);
-                if (need && pix != kInvalidPixel) {
-                    // A8 result + A9 tonemap/pack, main.cpp:484-492
-                    const float mx = SRT_ST(S_MX, r), my = SRT_ST(S_MY, r), mz = SRT_ST(S_MZ, r);
-                    P.accum[pix] = make_float4(mx, my, mz, 1.0f);
-                    if (P.accum_mode == SRT_ACCUM_MEAN) P.rgba[pix] = pack_rgba8(mx, my, mz);
-                    pix = kInvalidPixel;
-                }
-                unsigned m = __ballot_sync(0xFFFFFFFFu, need);
-                while (m) {
-                    const unsigned leader = __ffs(m) - 1;
-                    unsigned base = 0;
-                    if (lane == leader) base = atomicAdd(P.work_counter, __popc(m));
-                    base = __shfl_sync(0xFFFFFFFFu, base, leader);
-                    if (need) {
-                        const uint32_t item = base + __popc(m & ((1u << lane) - 1u));
-                        uint32_t px, py;
-                        if (item >= P.total_items) { flags |= kFlagDone; need = false; }
-                        else if (item_to_pixel(P, item, px, py)) {
-                            pix = py * P.width + px;
-                            pxy = px | (py << 16);
-                            k = P.first_sample;
-                            need = false;
-                            float4 prev = make_float4(0.0f, 0.0f, 0.0f, 0.0f);   // PreviousColor * (0/1), zeroed arena
-                            if (P.first_sample > 0 || P.accum_mode == SRT_ACCUM_SUM) prev = P.accum[pix];
-                            SRT_ST(S_MX, r) = prev.x; SRT_ST(S_MY, r) = prev.y; SRT_ST(S_MZ, r) = prev.z;
-                        }
-                    }
-                    m = __ballot_sync(0xFFFFFFFFu, need);
-                }
-                if (idle) {
-                    f3 o = mk3(kIdleOrigin, kIdleOrigin, kIdleOrigin), d = mk3(0.0f, 0.0f, 0.0f);   // out of work: parked
-                    if (!(flags & kFlagDone)) {
-                        uint64_t rng;
-                        primary_ray<true>(P, pxy & 0xFFFFu, pxy >> 16, pix, k, rng, o, d);
-                        SRT_ST(S_AX, r) = 1.0f; SRT_ST(S_AY, r) = 1.0f; SRT_ST(S_AZ, r) = 1.0f;
-                        SRT_ST(S_LX, r) = 0.0f; SRT_ST(S_LY, r) = 0.0f; SRT_ST(S_LZ, r) = 0.0f;
-                        SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
-                        flags = kFlagActive;                                           // bounce 0
-                    }
-                    SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
-                    SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
-                }
-                SRT_SU(S_PIX, r) = pix; SRT_SU(S_K, r) = k; SRT_SU(S_PXY, r) = pxy; SRT_SU(S_FLAGS, r) = flags;
-            }
-            all_done = all_done && (flags & kFlagDone);
-        }
-        if (__all_sync(0xFFFFFFFFu, all_done)) break;
-
-        // ---- A3/A4 brute-force intersection over ALL spheres, both slots at once ------------
-        Hit h0, h1;
-        {
-            const pk2 *const ray = reinterpret_cast<const pk2 *>(st);
-            const pk2 ox = ray[S_OX * THREADS + tid], oy = ray[S_OY * THREADS + tid], oz = ray[S_OZ * THREADS + tid];
-            const pk2 dx = ray[S_DX * THREADS + tid], dy = ray[S_DY * THREADS + tid], dz = ray[S_DZ * THREADS + tid];
-            intersect_pair<W, FMA>(s_scan, s_r2, P.spheres, P.n_pad, P.n_spheres, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, h0, h1);
-        }
-
-        // ---- shade / scatter, one slot after the other ---------------------------------------
-#pragma unroll 1
-        for (int r = 0; r < 2; ++r) {
-            uint32_t flags = SRT_SU(S_FLAGS, r);
-            if (!(flags & kFlagActive)) continue;
-            rays += 1;                                                        // main.cpp:390
-            const Hit h = r ? h1 : h0;
-            const uint32_t k = SRT_SU(S_K, r);
-            uint32_t bounce = flags & kFlagBounceMask;
-            f3 o = mk3(SRT_ST(S_OX, r), SRT_ST(S_OY, r), SRT_ST(S_OZ, r));
-            f3 d = mk3(SRT_ST(S_DX, r), SRT_ST(S_DY, r), SRT_ST(S_DZ, r));
-            f3 atten = mk3(SRT_ST(S_AX, r), SRT_ST(S_AY, r), SRT_ST(S_AZ, r));
-            f3 out = mk3(SRT_ST(S_LX, r), SRT_ST(S_LY, r), SRT_ST(S_LZ, r));
-            uint64_t rng = (uint64_t)SRT_SU(S_RNG_LO, r) | ((uint64_t)SRT_SU(S_RNG_HI, r) << 32);
-            if (bounce == 0 && P.tap_t != nullptr && k == P.first_sample) {
-                const uint32_t pix = SRT_SU(S_PIX, r);
-                P.tap_t[pix] = h.t;
-                P.tap_prim[pix] = h.prim;
-            }
-            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (h.hit) s = s_scan[h.prim];                                    // centre only; .w is not used by shading
-            if (shade_scatter<true>(P, h, s, o, d, atten, out, rng, bounce)) {
-                const f3 mean = accumulate_sample(P.accum_mode, mk3(SRT_ST(S_MX, r), SRT_ST(S_MY, r), SRT_ST(S_MZ, r)), out, k);
-                SRT_ST(S_MX, r) = mean.x; SRT_ST(S_MY, r) = mean.y; SRT_ST(S_MZ, r) = mean.z;
-                SRT_SU(S_K, r) = k + P.sample_stride;
-                flags = 0u;                                                   // idle; regenerated next pass
-            } else {
-                SRT_SU(S_RNG_LO, r) = (uint32_t)rng; SRT_SU(S_RNG_HI, r) = (uint32_t)(rng >> 32);
-                SRT_ST(S_OX, r) = o.x; SRT_ST(S_OY, r) = o.y; SRT_ST(S_OZ, r) = o.z;
-                SRT_ST(S_DX, r) = d.x; SRT_ST(S_DY, r) = d.y; SRT_ST(S_DZ, r) = d.z;
-                SRT_ST(S_AX, r) = atten.x; SRT_ST(S_AY, r) = atten.y; SRT_ST(S_AZ, r) = atten.z;
-                SRT_ST(S_LX, r) = out.x; SRT_ST(S_LY, r) = out.y; SRT_ST(S_LZ, r) = out.z;
-                flags = kFlagActive | bounce;
-            }
-            SRT_SU(S_FLAGS, r) = flags;
-        }
-    }
-#undef SRT_ST
-#undef SRT_SU
-
-    // rays: one atomic per warp
-    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
-    if (lane == 0 && rays) atomicAdd(P.rays, rays);
-}
+constexpr uint32_t kFlagBounceMask = 7u, kFlagPending = 32u;
 
 // ------------------------------------------------------------------------------------------
-// render_pool: render_pairs with the path slots owned by the CTA (srt_pool.cuh).  A warp pass
-// is either 64 PRIMARY rays (regenerate + 4-FFMA2 filter) or 64 SECONDARY rays (7-FFMA2 filter).
+// render_pool: TWO paths per thread in the halves of the f32x2 instructions (srt_pairs.cuh), path slots
+// owned by the CTA (srt_pool.cuh).  A warp pass is either 64 slots that need a NEW PRIMARY ray (fetch work
+// items, regenerate; in bundle mode all samples of one pixel, srt_bundle.cuh) or 64 slots with a SECONDARY
+// ray ready; both run level 1 (slab test of every sphere) -> level 2 (7-FMA filter) -> exact select -> shade.
 // ------------------------------------------------------------------------------------------
 // Slab table entry of sphere i (srt_pairs.cuh): kept-axis coordinates and the inflated radius.
 __device__ __forceinline__ void slab_entry(float *table, uint32_t i, float4 c, float r2, bool real, int axis, float omax) {
     const float cp = axis == 0 ? c.y : (axis == 1 ? c.z : c.x), cq = axis == 0 ? c.z : (axis == 1 ? c.x : c.y);
     float *g = table + (i >> 2) * 12u + (i & 3u);
-    g[0] = cp; g[4] = cq; g[8] = real ? slab_radius(r2, c.x, c.y, c.z, omax) : -1.0f;
+    g[0] = cp; g[4] = cq; g[8] = real ? slab_radius(r2, c.x, c.y, c.z, omax) : kSlabPadRadius;
 }
 // Streamed scenes: the slab table is built once per launch in global memory.
 __global__ void build_slab_kernel(const float4 *scan, const float4 *spheres, float *table, uint32_t n_pad, uint32_t n_real, int axis, float omax) {
@@ -748,11 +605,9 @@ render_pool(const __grid_constant__ KernelParams P) {
 #undef SRT_ST
 #undef SRT_SU
 
-    // rays: one atomic per warp
-    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
-    if (lane == 0 && rays) atomicAdd(P.rays, rays);
     __syncthreads();
     if (tid == 0 && P.debug) { atomicAdd(&P.debug[0], (unsigned long long)ctl->spins_steady); atomicAdd(&P.debug[1], (unsigned long long)ctl->spins_tail); }
+    finish_launch(P, rays);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -785,7 +640,7 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
                 for (uint32_t i = 0; i < P.n_pad; ++i) {
                     const float4 s = P.spheres[i];
                     const float cp = P.slab_axis == 0 ? s.y : (P.slab_axis == 1 ? s.z : s.x), cq = P.slab_axis == 0 ? s.z : (P.slab_axis == 1 ? s.x : s.y);
-                    const bool slab = slab_test(cp, cq, i < P.n_spheres ? slab_radius(s.w, s.x, s.y, s.z, P.omax) : -1.0f, sl);
+                    const bool slab = slab_test(cp, cq, i < P.n_spheres ? slab_radius(s.w, s.x, s.y, s.z, P.omax) : kSlabPadRadius, sl);
                     const float scx = __fsub_rn(s.x, o.x), scy = __fsub_rn(s.y, o.y), scz = __fsub_rn(s.z, o.z);
                     const float t = lane_dot<(W != 1) && FMA>(scx, scy, scz, d.x, d.y, d.z);
                     const float vx = __fsub_rn(scx, __fmul_rn(d.x, t));
@@ -801,7 +656,7 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
                     n_cand += (slab && mask) ? 1 : 0;
                     n_viol += (exact && !(slab && mask)) ? 1 : 0;
                     if (bounce == 0 && !(bp.eps < 0.0f)) {             // a pixel with eps < 0 takes the per-ray scan
-                        const bool bund = bundle_test(cp, cq, i < P.n_spheres ? slab_radius(s.w, s.x, s.y, s.z, P.omax) : -1.0f, P.cam.pos[ip], P.cam.pos[iq], bp);
+                        const bool bund = bundle_test(cp, cq, i < P.n_spheres ? slab_radius(s.w, s.x, s.y, s.z, P.omax) : kSlabPadRadius, P.cam.pos[ip], P.cam.pos[iq], bp);
                         n_btests += 1;
                         n_bcand += bund ? 1 : 0;
                         n_bviol += (exact && !bund) ? 1 : 0;
@@ -836,6 +691,57 @@ audit_filter(const __grid_constant__ KernelParams P, unsigned long long *counter
         atomicAdd(&counters[6], n_bcand);
         atomicAdd(&counters[7], n_bviol);
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// kat_kernel: diagnostic behind srt_device_kat().  Runs the device functions the render kernels are built
+// from -- pcg_next / rand_float (base.h:954-989), stream_seed (main.cpp:667-676), normalize3
+// (x64_math.h:234-245), reflectance (main.cpp:292-300), linear_to_srgb / pack_rgba8 (main.cpp:312-346) --
+// on caller-provided inputs, one record per thread, so that the reference's known answers
+// (tests/golden/ref_kat.json), edge values included, are checked on the GPU and not only through images.
+// ------------------------------------------------------------------------------------------
+__global__ void kat_kernel(uint32_t op, const void *in, uint32_t n, void *out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    switch (op) {
+        case SRT_KAT_PCG: {                       // in: u64 seed -> out: 16 x u32
+            uint64_t s = ((const uint64_t *)in)[i];
+            for (int j = 0; j < 16; ++j) ((uint32_t *)out)[i * 16u + j] = pcg_next(s);
+        } break;
+        case SRT_KAT_RANDOM_FLOAT: {              // in: {u64 seed, f32 inverse_max_int, f32 min} -> out: 16 x f32
+            const uint64_t *rec = (const uint64_t *)in + 2u * i;
+            uint64_t s = rec[0];
+            const float inv = __uint_as_float((uint32_t)rec[1]), mn = __uint_as_float((uint32_t)(rec[1] >> 32));
+            for (int j = 0; j < 16; ++j) ((float *)out)[i * 16u + j] = rand_float(s, inv, mn);
+        } break;
+        case SRT_KAT_STREAM_SEED:                 // in: u64 index -> out: u64
+            ((uint64_t *)out)[i] = stream_seed(((const uint64_t *)in)[i]);
+            break;
+        case SRT_KAT_NORMALIZE: {                 // in: 3 x f32 -> out: 3 x f32
+            const float *v = (const float *)in + 3u * i;
+            const f3 r = normalize3(mk3(v[0], v[1], v[2]));
+            float *o = (float *)out + 3u * i;
+            o[0] = r.x; o[1] = r.y; o[2] = r.z;
+        } break;
+        case SRT_KAT_REFLECTANCE: {               // in: {cos, eta} -> out: f32
+            const float *v = (const float *)in + 2u * i;
+            ((float *)out)[i] = reflectance(v[0], v[1]);
+        } break;
+        case SRT_KAT_LINEAR_TO_SRGB:              // in: f32 -> out: f32
+            ((float *)out)[i] = linear_to_srgb(((const float *)in)[i]);
+            break;
+        case SRT_KAT_PACK: {                      // in: 4 x f32 {r, g, b, -} -> out: u32 RGBA8
+            const float *v = (const float *)in + 4u * i;
+            ((uint32_t *)out)[i] = pack_rgba8(v[0], v[1], v[2]);
+        } break;
+        default: break;
+    }
+}
+
+// srt_write_accum on a partitioned handle: keep the rows this device owns (block row by = py / 4 with by % n_parts == part).
+__global__ void clear_foreign_rows(float4 *accum, uint32_t width, uint32_t n_pixels, uint32_t part, uint32_t n_parts) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_pixels && ((i / width) >> 2) % n_parts != part) accum[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
 }
 
 // mean = sum * (1/N); tonemap + pack.  HBM-bound: 16 B read + 16 B + 4 B written per pixel.
@@ -874,22 +780,56 @@ __global__ void __launch_bounds__(256) resolve_sum_kernel_1px(float4 *accum, uin
 // =============================================================================================
 using namespace srt;
 
+// Diagnostic knobs (environment), read ONCE per srt_set_scene -- never on the per-frame path.
+struct Knobs {
+    int variant = 0;                     // SRT_KERNEL_VARIANT: 0 auto (pool kernel from 64 spheres, else one path per thread);
+                                         // 1 scalar-issue loop; 7 force one path per thread; 9 force the pool kernel; 12 force
+                                         // the STREAMED pool kernel
+    int slab_axis = -1;                  // SRT_SLAB_AXIS: force the slab axis (0/1/2)
+    uint32_t pool_chunk = 0;             // SRT_POOL_CHUNK: samples per work item of the non-bundle pool kernel, 0 = kPoolChunkSamples
+    int bundle = 1;                      // SRT_BUNDLE: 1 auto (>= kBundleMinSamples samples, >= kBundleMinSpheres spheres), 0 off,
+                                         // k >= 2 forced with chunks of <= 2^k samples
+    int regen_threshold = 0;             // SRT_REGEN_THRESHOLD: 0 = automatic
+    int pool_threads = 0;                // SRT_POOL_THREADS: force the resident pool configuration (896 / 512 / 256)
+    bool pool_debug = false;             // SRT_POOL_DEBUG: print ring statistics after every launch (synchronous)
+    uint32_t band_rows = 0;              // SRT_BUNDLE_BAND_ROWS: block rows per staging band (tests: tiny bands)
+    size_t stage_limit = ~(size_t)0;     // SRT_BUNDLE_STAGE_LIMIT: pretend larger staging allocations fail (tests)
+    int resolve_variant = 0;             // SRT_RESOLVE_VARIANT: 1 = one pixel per thread
+};
+static Knobs read_knobs() {
+    Knobs k;
+    if (const char *v = getenv("SRT_KERNEL_VARIANT")) k.variant = atoi(v);
+    if (const char *v = getenv("SRT_SLAB_AXIS")) k.slab_axis = std::min(2, std::max(0, atoi(v)));
+    if (const char *v = getenv("SRT_POOL_CHUNK")) k.pool_chunk = (uint32_t)std::max(0, atoi(v));
+    if (const char *v = getenv("SRT_BUNDLE")) k.bundle = atoi(v);
+    if (const char *v = getenv("SRT_REGEN_THRESHOLD")) k.regen_threshold = std::min(32, std::max(1, atoi(v)));
+    if (const char *v = getenv("SRT_POOL_THREADS")) k.pool_threads = atoi(v);
+    k.pool_debug = getenv("SRT_POOL_DEBUG") != nullptr;
+    if (const char *v = getenv("SRT_BUNDLE_BAND_ROWS")) k.band_rows = (uint32_t)std::max(1, atoi(v));
+    if (const char *v = getenv("SRT_BUNDLE_STAGE_LIMIT")) k.stage_limit = (size_t)atoll(v);
+    if (const char *v = getenv("SRT_RESOLVE_VARIANT")) k.resolve_variant = atoi(v);
+    return k;
+}
+
+typedef void (*render_kernel_t)(const KernelParams);
+// Launch configuration of one (kernel, block size, shared memory) triple: the attribute calls and the occupancy query
+// are made once, not per frame (the per-frame kick replaces WorkQueueStart, main.cpp:852 -- it has to be cheap).
+struct LaunchCfg { render_kernel_t kernel; int threads; size_t smem; int per_sm; };
+
 struct srt_backend {
     int device = -1;
     int sm_count = 0, clock_khz = 0;
     size_t max_smem_optin = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stop = nullptr;
+    bool events_recorded = false;
     // scene
     float4 *d_spheres = nullptr;         // {cx,cy,cz,r2} per sphere (scalar-issue kernels)
     float4 *d_spheres2 = nullptr;        // sphere-pair layout (packed f32x2 kernels)
-    float4 *d_scan = nullptr;            // filter table of the ray-pair kernel {cx,cy,cz,-kappa}
-    float4 *d_ptab = nullptr;            // primary-ray filter table of streamed scenes (rebuilt per launch)
+    float4 *d_scan = nullptr;            // filter table of the pool kernel {cx,cy,cz,-kappa}
+    float4 *d_ptab = nullptr;            // slab table of streamed scenes (rebuilt per launch)
     DevMaterial *d_materials = nullptr;
-    int variant = 0;                     // 0: auto (pool kernel from 64 spheres, else sphere-pair); 1: scalar-issue loop;
-                                         // 2..6: sphere-pair tuning; 7: force sphere-pair; 8: force ray-pair kernel with
-                                         // thread-owned slots; 9: force pool kernel; 12: force the STREAMED pool kernel
-                                         // (diagnostics, SRT_KERNEL_VARIANT)
+    Knobs knobs;
     uint32_t regen_threshold = 1;
     uint32_t n_spheres = 0, n_pad = 0;
     srt_scene_options opt = {0, 8, 1, 0};
@@ -900,23 +840,33 @@ struct srt_backend {
     uint32_t *d_tap_prim = nullptr;
     float *d_tap_t = nullptr;
     bool tap_valid = false;
-    // counters: [0..7] rays (u64), [8..11] work counter
+    // image partition over devices (srt_set_partition): this handle renders block rows by = part + k * n_parts
+    uint32_t part = 0, n_parts = 1;
+    // counters: [0..7] rays (u64), [8..11] work counter, [12..15] exit ticket, [16..63] diagnostics.  The last CTA of a
+    // launch publishes the ray count to pinned host memory and re-arms the counters (finish_launch): no memset / copy per frame.
     unsigned char *d_counters = nullptr;
+    bool counters_dirty = true;          // first launch, or a failed one: memset before the next launch
     uint32_t *d_done = nullptr;          // pool kernel: per-pixel chunk counters (KernelParams::done)
+    uint32_t pool_seq = 0;               // pool launches issued: done-tag sequence (20 bits, 0xFFFFF reserved for the 0xFF fill)
     int slab_axis = 1;                   // axis contained in the slab planes: least spread of the centres
     double omax_scene = 0.0;             // >= |C| + r of every sphere (bound on secondary-ray origins)
-    uint32_t pool_chunk = 0;             // samples per work item, 0 = kPoolChunkSamples (SRT_POOL_CHUNK)
-    int bundle = 1;                      // bundle mode of the pool kernel: 1 = auto (>= kBundleMinSamples samples, >= kBundleMinSpheres
-                                         // spheres), 0 = off, k >= 2 = forced with chunks of <= 2^k samples (SRT_BUNDLE)
     float4 *d_stage = nullptr;           // bundle mode: staging rows of the pixels in flight (KernelParams::stage)
     uint32_t *d_cnt = nullptr;           // bundle mode: samples staged per row
     size_t stage_bytes = 0, cnt_rows = 0;
     float2 *d_fold_w = nullptr;          // bundle mode: running-mean weights of the launch's samples
     uint32_t fold_w_cap = 0;
+    uint32_t fold_w_first = 0, fold_w_n = 0, fold_w_stride = 0;   // what d_fold_w currently holds
     std::vector<float2> h_fold_w;
-    unsigned long long *h_rays = nullptr;   // pinned
+    unsigned long long *h_rays = nullptr;   // pinned + mapped: written by the last CTA of a launch
+    std::vector<LaunchCfg> cfgs;
     bool in_flight = false;
     uint64_t launches = 0;
+    // multi-device (srt_comm_*): NCCL communicator of this handle, gather buffers on the root
+    void *comm = nullptr;
+    int comm_rank = 0, comm_size = 1;
+    uint32_t *d_gather_rgba = nullptr;
+    float4 *d_gather_accum = nullptr;
+    bool gathered_rgba = false, gathered_accum = false;
     std::string err;
 };
 
@@ -933,23 +883,14 @@ static int fail(srt_backend *b, int code, const std::string &msg) {
             return fail((b), SRT_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_)); \
     } while (0)
 
-typedef void (*render_kernel_t)(const KernelParams);
-static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed, int variant) {
-    if (variant >= 2 && o.lane_width == 8 && o.fma_dot) {     // tuning experiments (W=8, FMA only)
-        switch (variant) {
-            case 2: return render_paths<8, true, true, 4, 3>;
-            case 5: return render_paths<8, true, true, 4, 4>;
-            case 6: return render_paths<8, true, false, 4, 5>;
-            default: break;
-        }
-    }
-    // Tiny scenes are shading- and latency-bound: more resident warps beat the 104-register configuration (2 CTAs per SM).
-    // Demo scene, 1080p: scalar-issue loop at 4 CTAs / SM 32.7 Grays/s at 64 spp and 0.139 ms at 1 spp; packed loop at
-    // 3 CTAs / SM 31.4 and 0.147; before 27.3 and 0.193.  (A packed body must cover whole SIMD groups: 2 * PAIRS % W == 0.)
-    if (variant == 13) {                                       // the previous configuration, for A/B runs
-        if (o.lane_width == 1) return render_paths<1, false, false>;
-        if (o.lane_width == 8 && o.fma_dot) return packed ? render_paths<8, true, true> : render_paths<8, true, false>;
-    }
+// One path per thread (render_paths): tiny scenes are shading- and latency-bound, more resident warps beat the
+// 104-register configuration.  Demo scene, 1080p: scalar-issue loop at 4 CTAs / SM 32.7 Grays/s at 64 spp and 0.139 ms at
+// 1 spp; packed loop at 3 CTAs / SM 31.4 and 0.147.  (A packed body must cover whole SIMD groups: 2 * PAIRS % W == 0.)
+static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed) {
+#ifdef SRT_FAST_BUILD                       // development / debug builds: only the lane_width 8 + FMA profile is compiled
+    if (o.lane_width != 8 || !o.fma_dot) return nullptr;
+    return packed ? render_paths<8, true, true, 4, 3> : render_paths<8, true, false, 4, 4>;
+#else
     if (o.lane_width == 1) return render_paths<1, false, false, 4, 4>;
     if (packed) {
         if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, true, 2, 4> : render_paths<4, false, true, 2, 4>;
@@ -957,38 +898,32 @@ static render_kernel_t pick_kernel(const srt_scene_options &o, bool packed, int 
     }
     if (o.lane_width == 4) return o.fma_dot ? render_paths<4, true, false, 4, 4> : render_paths<4, false, false, 4, 4>;
     return o.fma_dot ? render_paths<8, true, false, 4, 4> : render_paths<8, false, false, 4, 4>;
+#endif
 }
 
-// Ray-pair kernel (srt_pairs.cuh): used when the scene is large enough for the intersection
-// loop to dominate and small enough for the sphere tables to stay resident in shared memory.
-constexpr int kPairThreads = 256;
-constexpr int kPairMinBlocks = 2;
-constexpr uint32_t kPairsMinSpheres = 64;
-struct PairConfig { int threads; render_kernel_t kernel; };
-static PairConfig pick_pairs_kernel(const srt_scene_options &o) {
-    if (o.lane_width == 1) return {kPairThreads, render_pairs<1, false, kPairThreads, kPairMinBlocks>};
-    if (o.lane_width == 4) return {kPairThreads, o.fma_dot ? render_pairs<4, true, kPairThreads, kPairMinBlocks> : render_pairs<4, false, kPairThreads, kPairMinBlocks>};
-    return {kPairThreads, o.fma_dot ? render_pairs<8, true, kPairThreads, kPairMinBlocks> : render_pairs<8, false, kPairThreads, kPairMinBlocks>};
-}
-// Pool kernel (srt_pool.cuh): CTA-owned path slots, primary / secondary warp passes.
-// Pool kernel configurations.  Resident tables: one large CTA per SM -- the refine / select / shade
-// phases of a pass are latency-bound, the slab scan is issue-bound, and only warps in the scan keep
-// the issue port busy: 28 warps (72 registers) beat 16 warps (2 x 256 threads) by 24 % on the
-// 1,024-sphere scene.  Larger scenes trade warps for table space; beyond that the tables are streamed.
+// Pool kernel (srt_pool.cuh): CTA-owned path slots, primary / secondary warp passes; used from kPoolMinSpheres
+// spheres, where the intersection loop dominates.  Resident tables: one large CTA per SM -- the refine / select /
+// shade phases of a pass are latency-bound, the slab scan is issue-bound, and only warps in the scan keep the issue
+// port busy: 28 warps (72 registers) beat 16 warps (2 x 256 threads) by 24 % on the 1,024-sphere scene.  Larger
+// scenes trade warps for table space; beyond that the tables are streamed (2 CTAs of 256 threads).
+constexpr uint32_t kPoolMinSpheres = 64;
 constexpr int kPoolThreads = 256;           // streamed kernel: 2 CTAs of 256 threads
 constexpr int kPoolMinBlocks = 2;
 constexpr uint32_t kPoolChunkSamples = 1;   // samples per pool work item (measured best: 1; SRT_POOL_CHUNK overrides)
 constexpr int kPoolResidentThreads[3] = {896, 512, 256};
 template <int THREADS, int MINB, bool STREAM, bool BUNDLE>
 static render_kernel_t pick_pool_kernel_cfg(const srt_scene_options &o) {
+#ifdef SRT_FAST_BUILD
+    if (o.lane_width != 8 || !o.fma_dot) return nullptr;
+    return render_pool<8, true, THREADS, MINB, STREAM, BUNDLE>;
+#else
     if (o.lane_width == 1) return render_pool<1, false, THREADS, MINB, STREAM, BUNDLE>;
     if (o.lane_width == 4) return o.fma_dot ? render_pool<4, true, THREADS, MINB, STREAM, BUNDLE> : render_pool<4, false, THREADS, MINB, STREAM, BUNDLE>;
     return o.fma_dot ? render_pool<8, true, THREADS, MINB, STREAM, BUNDLE> : render_pool<8, false, THREADS, MINB, STREAM, BUNDLE>;
+#endif
 }
 template <bool BUNDLE>
 static render_kernel_t pick_pool_kernel_b(const srt_scene_options &o, bool stream, int threads) {
-    if (stream && threads == 768 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 768, 1, true, BUNDLE>;   // experiment
-    if (stream && threads == 512 && o.lane_width == 8 && o.fma_dot) return render_pool<8, true, 512, 1, true, BUNDLE>;   // experiment
     if (stream) return pick_pool_kernel_cfg<kPoolThreads, kPoolMinBlocks, true, BUNDLE>(o);
     if (threads == 896) return pick_pool_kernel_cfg<896, 1, false, BUNDLE>(o);
     if (threads == 512) return pick_pool_kernel_cfg<512, 1, false, BUNDLE>(o);
@@ -1003,9 +938,6 @@ static size_t pool_smem_bytes(uint32_t n_pad, int threads, bool stream, bool bun
     if (stream) bytes += warps * kStreamStages * (kStreamStageF4 * sizeof(float4) + sizeof(uint64_t));
     else bytes += (size_t)n_pad * (sizeof(float4) + 12 + sizeof(float));   // {c,-kappa}, slab table, r2
     return bytes;
-}
-static size_t pairs_smem_bytes(uint32_t n_pad, int threads) {
-    return (size_t)n_pad * (sizeof(float4) + sizeof(float)) + (size_t)S_COUNT * 2 * threads * sizeof(float);
 }
 
 // Bundle mode (srt_bundle.cuh).
@@ -1041,9 +973,44 @@ static double bundle_footprint(const srt_camera *cam, uint32_t width, uint32_t h
     return sqrt(a2 + b2 + cross) * 1.001 + fp_err;
 }
 
+static void comm_release(srt_backend *b) {
+    if (b->comm) {
+        NcclApi &N = nccl_api();
+        if (N.CommDestroy) N.CommDestroy((ncclComm_t)b->comm);
+        b->comm = nullptr;
+    }
+    b->comm_rank = 0;
+    b->comm_size = 1;
+}
+#define SRT_NCCL(b, call)                                                                                         \
+    do {                                                                                                          \
+        ncclResult_t r_ = (call);                                                                                 \
+        if (r_ != ncclSuccess)                                                                                    \
+            return fail((b), SRT_ERR_COMM, std::string(#call) + ": " + (nccl_api().GetErrorString ? nccl_api().GetErrorString(r_) : "NCCL error")); \
+    } while (0)
+
 extern "C" {
 
 const char *srt_last_error(const srt_backend *b) { return b ? b->err.c_str() : g_create_error.c_str(); }
+
+static int create_resources(srt_backend *b) {
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    SRT_CUDA(b, cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
+    SRT_CUDA(b, cudaEventCreate(&b->ev_start));
+    SRT_CUDA(b, cudaEventCreate(&b->ev_stop));
+    SRT_CUDA(b, cudaMalloc(&b->d_counters, 64));
+    SRT_CUDA(b, cudaMemset(b->d_counters, 0, 64));
+    SRT_CUDA(b, cudaHostAlloc(&b->h_rays, 2 * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
+    b->h_rays[0] = 0;                    // [0] rays of the last launch, [1] spin-limit report of the debug build
+    b->h_rays[1] = 0;
+#ifdef SRT_SPIN_LIMIT
+    {
+        unsigned long long *report = b->h_rays + 1;
+        SRT_CUDA(b, cudaMemcpyToSymbol(g_spin_report, &report, sizeof(report)));
+    }
+#endif
+    return SRT_OK;
+}
 
 int srt_create(srt_backend **out, int device_id) {
     if (!out) return fail(nullptr, SRT_ERR_INVALID, "srt_create: out is NULL");
@@ -1063,15 +1030,14 @@ int srt_create(srt_backend **out, int device_id) {
     b->sm_count = prop.multiProcessorCount;
     b->clock_khz = prop.clockRate;
     b->max_smem_optin = prop.sharedMemPerBlockOptin;
+    b->knobs = read_knobs();
+    const int rc = create_resources(b);
+    if (rc != SRT_OK) {                  // no half-built handle leaves this function: *out stays NULL, the reason is srt_last_error(NULL)
+        g_create_error = "srt_create: " + b->err;
+        srt_destroy(b);
+        return rc;
+    }
     *out = b;
-    SRT_CUDA(b, cudaSetDevice(device_id));
-    SRT_CUDA(b, cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
-    SRT_CUDA(b, cudaEventCreate(&b->ev_start));
-    SRT_CUDA(b, cudaEventCreate(&b->ev_stop));
-    SRT_CUDA(b, cudaMalloc(&b->d_counters, 64));
-    SRT_CUDA(b, cudaMemset(b->d_counters, 0, 64));
-    SRT_CUDA(b, cudaMallocHost(&b->h_rays, sizeof(unsigned long long)));
-    *b->h_rays = 0;
     return SRT_OK;
 }
 
@@ -1079,11 +1045,13 @@ void srt_destroy(srt_backend *b) {
     if (!b) return;
     cudaSetDevice(b->device);
     if (b->stream) cudaStreamSynchronize(b->stream);
+    comm_release(b);
     cudaFree(b->d_spheres); cudaFree(b->d_spheres2); cudaFree(b->d_scan); cudaFree(b->d_ptab); cudaFree(b->d_materials);
     cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own);
     cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t);
     cudaFree(b->d_counters);
     cudaFree(b->d_done); cudaFree(b->d_stage); cudaFree(b->d_cnt); cudaFree(b->d_fold_w);
+    cudaFree(b->d_gather_rgba); cudaFree(b->d_gather_accum);
     if (b->h_rays) cudaFreeHost(b->h_rays);
     if (b->ev_start) cudaEventDestroy(b->ev_start);
     if (b->ev_stop) cudaEventDestroy(b->ev_stop);
@@ -1166,8 +1134,9 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
                 if (a == 0 || var < best) { best = var; axis = a; }
             }
         }
-        b->slab_axis = axis;
-        if (const char *v = getenv("SRT_SLAB_AXIS")) b->slab_axis = std::min(2, std::max(0, atoi(v)));
+        b->knobs = read_knobs();                 // the only place the SRT_* diagnostics are read after srt_create
+        if (b->knobs.variant == 0) b->knobs.variant = options->_reserved;
+        b->slab_axis = b->knobs.slab_axis >= 0 ? b->knobs.slab_axis : axis;
         b->omax_scene = omax * 1.01 + 1e-3;
     }
     cudaFree(b->d_spheres); b->d_spheres = nullptr;
@@ -1187,19 +1156,12 @@ int srt_set_scene(srt_backend *b, const srt_sphere *spheres, uint32_t n_spheres,
     b->n_spheres = n_spheres;
     b->n_pad = n_pad;
     b->opt = *options;
-    b->variant = options->_reserved;
-    if (const char *v = getenv("SRT_KERNEL_VARIANT")) b->variant = atoi(v);
-    b->pool_chunk = 0;
-    if (const char *v = getenv("SRT_POOL_CHUNK")) b->pool_chunk = (uint32_t)std::max(0, atoi(v));
-    if (const char *v = getenv("SRT_BUNDLE")) b->bundle = atoi(v);
     // Path start-up costs the whole warp ~200 issue slots however few lanes need it.  For
     // tiny scenes (intersection pass cheaper than that) a warp therefore refills only once
     // all its lanes are idle, which also keeps its primary rays coherent; measured on B200:
     // scene 0 (5 spheres) 2.11 ms with 32 vs 2.43 ms with 1; 256+ spheres: 1 is best.
     b->regen_threshold = n_pad <= 16 ? 32u : (n_pad <= 32 ? 8u : 1u);
-    if (const char *t = getenv("SRT_REGEN_THRESHOLD")) b->regen_threshold = (uint32_t)atoi(t);
-    if (b->regen_threshold < 1) b->regen_threshold = 1;
-    if (b->regen_threshold > 32) b->regen_threshold = 32;
+    if (b->knobs.regen_threshold) b->regen_threshold = (uint32_t)b->knobs.regen_threshold;
     return SRT_OK;
 }
 
@@ -1211,19 +1173,24 @@ int srt_reset_accumulation(srt_backend *b) {
     SRT_CUDA(b, cudaMemsetAsync(b->d_accum, 0, n * sizeof(float4), b->stream));
     SRT_CUDA(b, cudaMemsetAsync(b->d_rgba, 0, n * sizeof(uint32_t), b->stream));
     b->tap_valid = false;
+    b->gathered_rgba = b->gathered_accum = false;
     return SRT_OK;
 }
 
 int srt_resize(srt_backend *b, uint32_t width, uint32_t height) {
     if (!b) return SRT_ERR_INVALID;
     if (width == 0 || height == 0) return fail(b, SRT_ERR_INVALID, "srt_resize: zero size");
-    if ((uint64_t)width * height > 0x7FFFFFFFull) return fail(b, SRT_ERR_TOO_LARGE, "srt_resize: image too large");
+    // pixel coordinates travel as px | py << 16 in the path slots, pixel indices as 32-bit words
+    if (width > 65535u || height > 65535u || (uint64_t)width * height > 0x7FFFFFFFull)
+        return fail(b, SRT_ERR_TOO_LARGE, "srt_resize: image too large (width, height <= 65535 and width * height < 2^31)");
     SRT_CUDA(b, cudaSetDevice(b->device));
     int rc = drain(b);
     if (rc) return rc;
     const size_t n = (size_t)width * height;
     if (width != b->width || height != b->height || !b->d_accum_own) {
         cudaFree(b->d_accum_own); cudaFree(b->d_rgba_own); cudaFree(b->d_tap_prim); cudaFree(b->d_tap_t); cudaFree(b->d_done);
+        cudaFree(b->d_gather_rgba); cudaFree(b->d_gather_accum);
+        b->d_gather_rgba = nullptr; b->d_gather_accum = nullptr;
         b->d_done = nullptr;
         b->d_accum_own = nullptr; b->d_rgba_own = nullptr; b->d_tap_prim = nullptr; b->d_tap_t = nullptr;
         SRT_CUDA(b, cudaMalloc(&b->d_accum_own, n * sizeof(float4)));
@@ -1262,7 +1229,7 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.spheres = b->d_spheres;
     P.scan_table = b->d_scan;
     P.regen_threshold = b->regen_threshold;
-    if (b->n_pad <= 16u && args->n_samples <= 2u && !getenv("SRT_REGEN_THRESHOLD")) P.regen_threshold = 16u;   // 1 spp / frame: 0.139 vs 0.158 ms
+    if (b->n_pad <= 16u && args->n_samples <= 2u && !b->knobs.regen_threshold) P.regen_threshold = 16u;   // 1 spp / frame: 0.139 vs 0.158 ms
     P.neg_one = -1.0f;
     P.one = 1.0f;
     P.materials = b->d_materials;
@@ -1283,7 +1250,11 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.div_bx = make_magic(P.blocks_x);
     P.two_over_w = 2.0f / (float)b->width;
     P.two_over_h = 2.0f / (float)b->height;
-    P.total_items = P.blocks_x * ((b->height + 3u) / 4u) * 32u;
+    // this handle's share of the image: block rows by = part + k * n_parts (srt_set_partition; the whole image by default)
+    const uint32_t blocks_y = (b->height + 3u) / 4u;
+    P.part = b->part;
+    P.n_parts = b->n_parts;
+    P.total_items = P.blocks_x * (blocks_y > b->part ? (blocks_y - b->part + b->n_parts - 1u) / b->n_parts : 0u) * 32u;
     P.first_sample = args->first_sample;
     P.n_samples = args->n_samples;
     P.sample_stride = args->sample_stride;
@@ -1293,6 +1264,8 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     P.rgba = b->d_rgba;
     P.rays = (unsigned long long *)b->d_counters;
     P.work_counter = (unsigned int *)(b->d_counters + 8);
+    P.ticket = (unsigned int *)(b->d_counters + 12);
+    P.host_rays = b->h_rays;
     P.debug = (unsigned long long *)(b->d_counters + 16);
     P.items_per_gen = P.total_items;
     P.chunk_span = 0;
@@ -1305,6 +1278,101 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     return SRT_OK;
 }
 
+// Attribute + occupancy calls of a (kernel, threads, shared memory) triple are made once per handle.
+static int launch_cfg(srt_backend *b, render_kernel_t kernel, int threads, size_t smem, int carve, int *per_sm) {
+    for (const LaunchCfg &c : b->cfgs)
+        if (c.kernel == kernel && c.threads == threads && c.smem == smem) { *per_sm = c.per_sm; return SRT_OK; }
+    SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (carve >= 0) SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+    int n = 0;
+    SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem));
+    if (n < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
+    b->cfgs.push_back({kernel, threads, smem, n});
+    *per_sm = n;
+    return SRT_OK;
+}
+
+// Bundle mode set-up of one launch (srt_bundle.cuh): staging bands, item decoding constants, fold weights.
+// Returns false (with P untouched where it matters) when this launch has to run without bundle mode.
+static int plan_bundle(srt_backend *b, const srt_camera *cam, const srt_render_args *args, KernelParams &P, bool *out_bundle) {
+    *out_bundle = false;
+    const Knobs &K = b->knobs;
+    // auto: scenes of >= kBundleMinSpheres (below that the per-ray scan is too short for the saving to pay for the
+    // staging and the larger code) and launches of >= kBundleMinSamples samples (8 spp +8 %, 4 spp -2 %);
+    // SRT_BUNDLE=0 off, =k >= 2 forces it
+    const bool want = K.bundle > 1 || (K.bundle == 1 && b->n_pad >= kBundleMinSpheres);
+    if (!want || args->n_samples < (K.bundle > 1 ? 4u : kBundleMinSamples) || K.pool_chunk || P.items_per_gen == 0u) return SRT_OK;
+    uint32_t blog = 0;
+    while (blog < 6u && (2u << blog) <= args->n_samples) ++blog;                 // S = min(64, 2^floor(log2 n))
+    if (K.bundle > 1) blog = std::min<uint32_t>(blog, (uint32_t)K.bundle);       // SRT_BUNDLE=k (k >= 2): S <= 2^k (tests)
+    const uint64_t S = 1ull << blog, n_chunks = (args->n_samples + S - 1) / S;
+    const double rho = bundle_footprint(cam, b->width, b->height, P.slab_axis);
+    // needs a sane pinhole camera (the footprint bound) and 32-bit item indices
+    if (!(rho > 0.0) || n_chunks > 4095 || (uint64_t)P.items_per_gen * n_chunks * S >= 0xF0000000ull) return SRT_OK;
+    // bands of whole block rows, as large as kBundleStageBytes of staging rows allow (SRT_BUNDLE_BAND_ROWS: tests,
+    // tiny bands).  Measured: larger bands are faster (4K / 256 spp: 2 block rows 6,353, 64 rows 6,525 Mrays/s;
+    // 65,536 spheres: 17 rows 155, whole image 190) -- a chunk's fold waits in ring F for 63 others, and the next
+    // chunk / band of the same staging row must not start before it; L2 residency of the rows does not matter.
+    const uint32_t row_items = P.blocks_x * 32u, blocks_y = P.items_per_gen / row_items;   // local block rows of this handle
+    uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)((kBundleStageBytes / (S * sizeof(float4))) / row_items));
+    if (K.band_rows) band_rows = K.band_rows;
+    band_rows = std::min(band_rows, blocks_y);
+    size_t rows = 0;
+    for (;;) {                                                // smaller bands if the device is short of memory
+        rows = (size_t)band_rows * row_items;
+        const size_t need = rows * S * sizeof(float4);
+        if (need <= b->stage_bytes && rows <= b->cnt_rows) break;
+        cudaFree(b->d_stage); cudaFree(b->d_cnt);
+        b->d_stage = nullptr; b->d_cnt = nullptr; b->stage_bytes = 0; b->cnt_rows = 0;
+        if (need <= K.stage_limit && cudaMalloc(&b->d_stage, need) == cudaSuccess && cudaMalloc(&b->d_cnt, rows * sizeof(uint32_t)) == cudaSuccess) {
+            b->stage_bytes = need;
+            b->cnt_rows = rows;
+            break;
+        }
+        cudaGetLastError();
+        cudaFree(b->d_stage); cudaFree(b->d_cnt);
+        b->d_stage = nullptr; b->d_cnt = nullptr;
+        if (band_rows == 1u) return SRT_OK;                   // not even one block row: this launch runs without bundle mode
+        band_rows = (band_rows + 1u) / 2u;
+    }
+    P.bundle_log2 = blog;
+    P.n_chunks = (uint32_t)n_chunks;
+    P.n_bands = (blocks_y + band_rows - 1) / band_rows;
+    P.band_items = band_rows * row_items;
+    P.band_last = P.items_per_gen - (P.n_bands - 1) * P.band_items;
+    P.band_pix = band_rows * 4u * b->width * b->n_parts;      // local block rows are n_parts block rows apart in the image
+    P.div_full = make_magic(P.band_items * P.n_chunks);
+    P.div_band = make_magic(P.band_items);
+    P.div_last = make_magic(P.band_last);
+    P.bundle_rho = (float)rho;
+    P.total_items = (uint32_t)((uint64_t)P.items_per_gen * n_chunks * S);
+    SRT_CUDA(b, cudaMemsetAsync(b->d_cnt, 0, rows * sizeof(uint32_t), b->stream));
+    P.stage = b->d_stage;
+    P.cnt = b->d_cnt;
+    if (args->accum_mode == SRT_ACCUM_MEAN) {                 // A8 weights of the launch's samples (main.cpp:484-487)
+        if (args->n_samples > b->fold_w_cap) {
+            cudaFree(b->d_fold_w);
+            b->d_fold_w = nullptr; b->fold_w_cap = 0; b->fold_w_n = 0;
+            SRT_CUDA(b, cudaMalloc(&b->d_fold_w, (size_t)args->n_samples * sizeof(float2)));
+            b->fold_w_cap = args->n_samples;
+        }
+        if (b->fold_w_n != args->n_samples || b->fold_w_first != args->first_sample || b->fold_w_stride != args->sample_stride) {
+            b->h_fold_w.resize(args->n_samples);
+            for (uint32_t i = 0; i < args->n_samples; ++i) {
+                const uint32_t k = args->first_sample + i * args->sample_stride;
+                const float total = (float)(k + 1u);
+                b->h_fold_w[i] = make_float2(1.0f / total, (float)k / total);
+            }
+            // pageable source: the copy has left h_fold_w when the call returns
+            SRT_CUDA(b, cudaMemcpyAsync(b->d_fold_w, b->h_fold_w.data(), (size_t)args->n_samples * sizeof(float2), cudaMemcpyHostToDevice, b->stream));
+            b->fold_w_n = args->n_samples; b->fold_w_first = args->first_sample; b->fold_w_stride = args->sample_stride;
+        }
+        P.fold_w = b->d_fold_w;
+    }
+    *out_bundle = true;
+    return SRT_OK;
+}
+
 int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *args) {
     if (!b) return SRT_ERR_INVALID;
     KernelParams P;
@@ -1313,26 +1381,27 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     SRT_CUDA(b, cudaSetDevice(b->device));
     rc = drain(b);
     if (rc) return rc;
+    b->gathered_rgba = b->gathered_accum = false;
+    if (P.total_items == 0u) {            // more devices than block rows: this handle owns no pixel
+        *b->h_rays = 0;
+        b->events_recorded = false;
+        return SRT_OK;
+    }
 
-    const PairConfig pc = pick_pairs_kernel(b->opt);
-    const bool pairs_fit = b->n_pad <= (uint32_t)kPairsMaxSpheres && pairs_smem_bytes(b->n_pad, pc.threads) <= b->max_smem_optin;
-    // kernel choice: tiny scenes -> one path per thread; otherwise the pool kernel, with the sphere
-    // tables resident in shared memory when they fit and streamed through per-warp TMA stages when not
-    // resident configuration with the most warps whose tables + path slots fit in shared memory
+    // kernel choice: tiny scenes -> one path per thread; otherwise the pool kernel, with the sphere tables resident
+    // in shared memory (the configuration with the most warps whose tables + path slots fit) or streamed through
+    // per-warp TMA stages when they do not fit
+    const Knobs &K = b->knobs;
     int pool_threads = 0;
     for (int t : kPoolResidentThreads) {
-        if (const char *v = getenv("SRT_POOL_THREADS")) { if (atoi(v) != t) continue; }
+        if (K.pool_threads && K.pool_threads != t) continue;
         if (b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, t, false) <= b->max_smem_optin) { pool_threads = t; break; }
     }
-    const bool pool_res_fit = pool_threads != 0;
-    const bool want_pool = b->variant == 9 || b->variant == 12 || (b->variant == 0 && b->n_pad >= kPairsMinSpheres);
-    const bool pool = want_pool;
-    const bool stream = pool && (b->variant == 12 || !pool_res_fit);
-    const bool pairs = !pool && b->variant == 8;
-    if (pairs && !pairs_fit) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the ray-pair kernel");
+    const bool pool = K.variant == 9 || K.variant == 12 || (K.variant == 0 && b->n_pad >= kPoolMinSpheres);
+    const bool stream = pool && (K.variant == 12 || pool_threads == 0);
     // <= 16 spheres (the demo scene): shading-bound, the scalar-issue loop at 4 CTAs per SM is the fastest valid configuration
-    const bool packed = !pool && !pairs && (b->variant != 1) && b->opt.lane_width != 1 && (b->n_pad > 16u || b->variant >= 2);
-    if (!pool && !pairs && (size_t)b->n_pad * sizeof(float4) > b->max_smem_optin)
+    const bool packed = !pool && K.variant != 1 && b->opt.lane_width != 1 && b->n_pad > 16u;
+    if (!pool && (size_t)b->n_pad * sizeof(float4) > b->max_smem_optin)
         return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the one-path kernel");
     if (packed) P.spheres = b->d_spheres2;
     if (args->record_primary) {
@@ -1347,128 +1416,58 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     }
 
     bool use_bundle = false;
-    const bool pool_debug = getenv("SRT_POOL_DEBUG") != nullptr;
-    if (!pool_debug) P.debug = nullptr;
+    if (!K.pool_debug) P.debug = nullptr;
     if (pool) {
         // work items = (sample chunk, pixel), chunk-major.  A pixel's chunks are folded in order through
         // done[pix]; short chunks keep the end of the launch short (few slots left with many samples to go).
-        if (!b->d_done) {   // 0xFF..: no launch tag matches (recycled device memory may hold another backend's counts)
-            SRT_CUDA(b, cudaMalloc(&b->d_done, (size_t)b->width * b->height * sizeof(uint32_t)));
-            SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
+        const size_t done_bytes = (size_t)b->width * b->height * sizeof(uint32_t);
+        bool done_fresh = false;
+        if (!b->d_done) {   // 0xFF..: tag 0xFFFFF is never issued (recycled device memory may hold another backend's counts)
+            SRT_CUDA(b, cudaMalloc(&b->d_done, done_bytes));
+            done_fresh = true;
         }
-        // bundle mode (srt_bundle.cuh): work items are single samples, 2^bundle_log2 consecutive samples of a pixel
-        // are consecutive items; needs a sane pinhole camera (the footprint bound below) and 32-bit item indices
-        bool bundle = false;
-        uint32_t blog = 0;
-        // auto: scenes of >= kBundleMinSpheres (below that the per-ray scan is too short for the saving to pay for the
-        // staging and the larger code) and launches of >= kBundleMinSamples samples (8 spp +8 %, 4 spp -2 %);
-        // SRT_BUNDLE=0 off, =k >= 2 forces it
-        const bool want_bundle = b->bundle > 1 || (b->bundle == 1 && b->n_pad >= kBundleMinSpheres);
-        if (want_bundle && args->n_samples >= (b->bundle > 1 ? 4u : kBundleMinSamples) && !b->pool_chunk) {
-            while (blog < 6u && (2u << blog) <= args->n_samples) ++blog;                 // S = min(64, 2^floor(log2 n))
-            if (b->bundle > 1) blog = std::min<uint32_t>(blog, (uint32_t)b->bundle);     // SRT_BUNDLE=k (k >= 2): S <= 2^k (tests)
-            const uint64_t S = 1ull << blog, n_chunks = (args->n_samples + S - 1) / S;
-            const double rho = bundle_footprint(cam, b->width, b->height, P.slab_axis);
-            if (rho > 0.0 && n_chunks <= 4095 && (uint64_t)P.items_per_gen * n_chunks * S < 0xF0000000ull) {
-                bundle = true;
-                // bands of whole block rows, as large as kBundleStageBytes of staging rows allow (SRT_BUNDLE_BAND_ROWS: tests,
-                // tiny bands).  Measured: larger bands are faster (4K / 256 spp: 2 block rows 6,353, 64 rows 6,525 Mrays/s;
-                // 65,536 spheres: 17 rows 155, whole image 190) -- a chunk's fold waits in ring F for 63 others, and the next
-                // chunk / band of the same staging row must not start before it; L2 residency of the rows does not matter.
-                const uint32_t row_items = P.blocks_x * 32u, blocks_y = P.items_per_gen / row_items;
-                uint32_t band_rows = std::max<uint32_t>(1u, (uint32_t)((kBundleStageBytes / (S * sizeof(float4))) / row_items));
-                if (const char *v = getenv("SRT_BUNDLE_BAND_ROWS")) band_rows = (uint32_t)std::max(1, atoi(v));
-                band_rows = std::min(band_rows, blocks_y);
-                size_t rows = 0, limit = ~(size_t)0;
-                if (const char *v = getenv("SRT_BUNDLE_STAGE_LIMIT")) limit = (size_t)atoll(v);   // tests: pretend larger allocations fail
-                for (;;) {                                                // smaller bands if the device is short of memory
-                    rows = (size_t)band_rows * row_items;
-                    const size_t need = rows * S * sizeof(float4);
-                    if (need <= b->stage_bytes && rows <= b->cnt_rows) break;
-                    cudaFree(b->d_stage); cudaFree(b->d_cnt);
-                    b->d_stage = nullptr; b->d_cnt = nullptr; b->stage_bytes = 0; b->cnt_rows = 0;
-                    if (need <= limit && cudaMalloc(&b->d_stage, need) == cudaSuccess && cudaMalloc(&b->d_cnt, rows * sizeof(uint32_t)) == cudaSuccess) {
-                        b->stage_bytes = need;
-                        b->cnt_rows = rows;
-                        break;
-                    }
-                    cudaGetLastError();
-                    cudaFree(b->d_stage); cudaFree(b->d_cnt);
-                    b->d_stage = nullptr; b->d_cnt = nullptr;
-                    if (band_rows == 1u) { bundle = false; break; }       // not even one block row: this launch runs without bundle mode
-                    band_rows = (band_rows + 1u) / 2u;
-                }
-                if (bundle) {
-                P.bundle_log2 = blog;
-                P.n_chunks = (uint32_t)n_chunks;
-                P.n_bands = (blocks_y + band_rows - 1) / band_rows;
-                P.band_items = band_rows * row_items;
-                P.band_last = P.items_per_gen - (P.n_bands - 1) * P.band_items;
-                P.band_pix = band_rows * 4u * b->width;
-                P.div_full = make_magic(P.band_items * P.n_chunks);
-                P.div_band = make_magic(P.band_items);
-                P.div_last = make_magic(P.band_last);
-                P.bundle_rho = (float)rho;
-                P.total_items = (uint32_t)((uint64_t)P.items_per_gen * n_chunks * S);
-                SRT_CUDA(b, cudaMemsetAsync(b->d_cnt, 0, rows * sizeof(uint32_t), b->stream));
-                P.stage = b->d_stage;
-                P.cnt = b->d_cnt;
-                if (args->accum_mode == SRT_ACCUM_MEAN) {                 // A8 weights of the launch's samples (main.cpp:484-487)
-                    if (args->n_samples > b->fold_w_cap) {
-                        cudaFree(b->d_fold_w);
-                        b->d_fold_w = nullptr; b->fold_w_cap = 0;
-                        SRT_CUDA(b, cudaMalloc(&b->d_fold_w, (size_t)args->n_samples * sizeof(float2)));
-                        b->fold_w_cap = args->n_samples;
-                    }
-                    b->h_fold_w.resize(args->n_samples);
-                    for (uint32_t i = 0; i < args->n_samples; ++i) {
-                        const uint32_t k = args->first_sample + i * args->sample_stride;
-                        const float total = (float)(k + 1u);
-                        b->h_fold_w[i] = make_float2(1.0f / total, (float)k / total);
-                    }
-                    SRT_CUDA(b, cudaMemcpyAsync(b->d_fold_w, b->h_fold_w.data(), (size_t)args->n_samples * sizeof(float2), cudaMemcpyHostToDevice, b->stream));
-                    P.fold_w = b->d_fold_w;
-                }
-                }
-            }
+        rc = plan_bundle(b, cam, args, P, &use_bundle);
+        if (rc) return rc;
+        if (!use_bundle) {
+            uint32_t chunk = K.pool_chunk ? K.pool_chunk : kPoolChunkSamples;
+            const uint32_t max_chunks = std::min<uint32_t>(4095u, 0xF0000000u / P.items_per_gen);
+            if ((args->n_samples + chunk - 1) / chunk > max_chunks) chunk = (args->n_samples + max_chunks - 1) / max_chunks;
+            const uint32_t n_chunks = (args->n_samples + chunk - 1) / chunk;
+            P.chunk_span = chunk * args->sample_stride;
+            P.total_items = P.items_per_gen * n_chunks;
+            P.n_chunks = n_chunks;
         }
-        use_bundle = bundle;
-        if (!bundle) {
-        uint32_t chunk = b->pool_chunk ? b->pool_chunk : kPoolChunkSamples;
-        const uint32_t max_chunks = std::min<uint32_t>(4095u, 0xF0000000u / P.items_per_gen);
-        if ((args->n_samples + chunk - 1) / chunk > max_chunks) chunk = (args->n_samples + max_chunks - 1) / max_chunks;
-        const uint32_t n_chunks = (args->n_samples + chunk - 1) / chunk;
-        P.chunk_span = chunk * args->sample_stride;
-        P.total_items = P.items_per_gen * n_chunks;
-        P.n_chunks = n_chunks;
-        }
+        // done[pix] = tag << 12 | chunks folded (<= 4095).  The tag is this handle's pool-launch sequence number modulo
+        // 0xFFFFF (a dedicated counter: other launches do not advance it); when it wraps, every count of the previous
+        // cycle is forgotten, whatever this launch's chunk count.
+        const uint32_t tag = b->pool_seq % 0xFFFFFu;
+        b->pool_seq = tag + 1u;
+        if (done_fresh || tag == 0u) SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, done_bytes, b->stream));
         P.done = b->d_done;
-        P.done_tag = (uint32_t)((b->launches + 1) & 0xFFFFFu) << 12;
-        if (P.done_tag == 0u && P.n_chunks > 1u)   // sequence wrapped: forget counts of 2^20 launches ago
-            SRT_CUDA(b, cudaMemsetAsync(b->d_done, 0xFF, (size_t)b->width * b->height * sizeof(uint32_t), b->stream));
+        P.done_tag = tag << 12;
     }
-    if (stream || !pool_res_fit) {
-        pool_threads = kPoolThreads;
-        if (const char *v = getenv("SRT_STREAM_THREADS")) { const int t = atoi(v); if ((t == 512 || t == 768) && b->opt.lane_width == 8 && b->opt.fma_dot) pool_threads = t; }
-    }
-    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, use_bundle) : pairs ? pc.kernel : pick_kernel(b->opt, packed, b->variant);
-    const int threads = pool ? pool_threads : pairs ? pc.threads : kBlockThreads;
-    const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream, use_bundle) : pairs ? pairs_smem_bytes(b->n_pad, pc.threads) : (size_t)b->n_pad * sizeof(float4);
-    SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (stream) pool_threads = kPoolThreads;
+    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, use_bundle) : pick_kernel(b->opt, packed);
+    if (!kernel) return fail(b, SRT_ERR_INVALID, "srt_render: this build (SRT_FAST_BUILD) only carries the lane_width 8 + FMA kernels");
+    const int threads = pool ? pool_threads : kBlockThreads;
+    const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream, use_bundle) : (size_t)b->n_pad * sizeof(float4);
+    int carve = -1;
     if (pool) {   // leave the rest of the 256 KB to L1: the candidate queues live in local memory
-        const size_t ctas = pool_threads == kPoolThreads && stream ? kPoolMinBlocks : 1;
-        const int carve = (int)std::min<size_t>(100, (ctas * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
-        SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        const size_t ctas = stream ? kPoolMinBlocks : 1;
+        carve = (int)std::min<size_t>(100, (ctas * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
     }
     int per_sm = 0;
-    SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem));
-    if (per_sm < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
+    rc = launch_cfg(b, kernel, threads, smem, carve, &per_sm);
+    if (rc) return rc;
     uint32_t grid = (uint32_t)(b->sm_count * per_sm);                 // persistent: one resident wave
-    const uint32_t paths_per_block = pool ? 64u * (threads / 32 + kPoolSpareBatches) : (uint32_t)threads * (pairs ? 2u : 1u);
+    const uint32_t paths_per_block = pool ? 64u * (threads / 32 + kPoolSpareBatches) : (uint32_t)threads;
     const uint32_t max_useful = (P.total_items + paths_per_block - 1) / paths_per_block;
     if (grid > max_useful) grid = max_useful;
 
-    SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 64, b->stream));
+    if (b->counters_dirty || K.pool_debug) {   // normally the previous launch's last CTA has re-armed the counters
+        SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 64, b->stream));
+        b->counters_dirty = false;
+    }
     SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
     if (stream) {
         P.ptab = b->d_ptab;
@@ -1477,12 +1476,13 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         b->launches += 1;
     }
     kernel<<<grid, threads, smem, b->stream>>>(P);
-    SRT_CUDA(b, cudaGetLastError());
+    const cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) { b->counters_dirty = true; return fail(b, SRT_ERR_CUDA, std::string("srt_render: launch: ") + cudaGetErrorString(le)); }
     SRT_CUDA(b, cudaEventRecord(b->ev_stop, b->stream));
-    SRT_CUDA(b, cudaMemcpyAsync(b->h_rays, b->d_counters, sizeof(unsigned long long), cudaMemcpyDeviceToHost, b->stream));
+    b->events_recorded = true;
     b->launches += 1;
     b->in_flight = true;
-    if (pool_debug) {
+    if (K.pool_debug) {
         unsigned long long dbg[6] = {0, 0, 0, 0, 0, 0};
         cudaStreamSynchronize(b->stream);
         cudaMemcpy(dbg, b->d_counters + 16, sizeof(dbg), cudaMemcpyDeviceToHost);
@@ -1504,14 +1504,25 @@ int srt_poll(srt_backend *b) {
 int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays) {
     if (!b) return SRT_ERR_INVALID;
     SRT_CUDA(b, cudaSetDevice(b->device));
-    SRT_CUDA(b, cudaStreamSynchronize(b->stream));
+    const cudaError_t e = cudaStreamSynchronize(b->stream);
     b->in_flight = false;
+    if (e != cudaSuccess) {
+        b->counters_dirty = true;
+        std::string msg = std::string("srt_wait: ") + cudaGetErrorString(e);
+        const unsigned long long rep = *(volatile unsigned long long *)(b->h_rays + 1);
+        if ((rep >> 48) == 0xDEADull) {      // -DSRT_SPIN_LIMIT build: a wait loop gave up (site: 1 ring pop, 2 ring push, 3 acquire, 4 TMA barrier)
+            char buf[96];
+            snprintf(buf, sizeof(buf), "; spin limit exceeded at site %u (CTA %u, thread %u)", (unsigned)((rep >> 32) & 0xFFFFu), (unsigned)((rep >> 12) & 0xFFFFFu), (unsigned)(rep & 0xFFFu));
+            msg += buf;
+        }
+        return fail(b, SRT_ERR_CUDA, msg);
+    }
     if (out_ms) {
         float ms = 0.f;
-        if (b->launches) SRT_CUDA(b, cudaEventElapsedTime(&ms, b->ev_start, b->ev_stop));
+        if (b->events_recorded) SRT_CUDA(b, cudaEventElapsedTime(&ms, b->ev_start, b->ev_stop));
         *out_ms = ms;
     }
-    if (out_rays) *out_rays = *b->h_rays;
+    if (out_rays) *out_rays = *(volatile unsigned long long *)b->h_rays;   // written by the last CTA of the last render
     return SRT_OK;
 }
 
@@ -1532,11 +1543,16 @@ int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_arg
     const uint32_t n = b->width * b->height;
     const dim3 grid((n + kBlockThreads - 1) / kBlockThreads);
     const srt_scene_options &o = b->opt;
+#ifdef SRT_FAST_BUILD
+    if (o.lane_width != 8 || !o.fma_dot) { cudaFree(d_cnt); return fail(b, SRT_ERR_INVALID, "srt_filter_audit: SRT_FAST_BUILD only carries lane_width 8 + FMA"); }
+    audit_filter<8, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+#else
     if (o.lane_width == 1) audit_filter<1, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     else if (o.lane_width == 4 && o.fma_dot) audit_filter<4, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     else if (o.lane_width == 4) audit_filter<4, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     else if (o.fma_dot) audit_filter<8, true><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
     else audit_filter<8, false><<<grid, kBlockThreads, 0, b->stream>>>(P, d_cnt);
+#endif
     cudaError_t e = cudaGetLastError();
     unsigned long long h[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_cnt, sizeof(h), cudaMemcpyDeviceToHost, b->stream);
@@ -1548,6 +1564,27 @@ int srt_filter_audit(srt_backend *b, const srt_camera *cam, const srt_render_arg
     return SRT_OK;
 }
 
+int srt_device_kat(srt_backend *b, uint32_t op, const void *in, uint32_t n, void *out) {
+    if (!b) return SRT_ERR_INVALID;
+    static const uint32_t in_bytes[SRT_KAT_COUNT] = {8, 16, 8, 12, 8, 4, 16}, out_bytes[SRT_KAT_COUNT] = {64, 64, 8, 12, 4, 4, 4};
+    if (op >= SRT_KAT_COUNT || !in || !out || n == 0) return fail(b, SRT_ERR_INVALID, "srt_device_kat: bad arguments");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    void *d_in = nullptr, *d_out = nullptr;
+    cudaError_t e = cudaMalloc(&d_in, (size_t)n * in_bytes[op]);
+    if (e == cudaSuccess) e = cudaMalloc(&d_out, (size_t)n * out_bytes[op]);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_in, in, (size_t)n * in_bytes[op], cudaMemcpyHostToDevice, b->stream);
+    if (e == cudaSuccess) {
+        kat_kernel<<<(n + 127) / 128, 128, 0, b->stream>>>(op, d_in, n, d_out);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, d_out, (size_t)n * out_bytes[op], cudaMemcpyDeviceToHost, b->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(b->stream);
+    cudaFree(d_in); cudaFree(d_out);
+    if (e != cudaSuccess) return fail(b, SRT_ERR_CUDA, std::string("srt_device_kat: ") + cudaGetErrorString(e));
+    b->launches += 1;
+    return SRT_OK;
+}
+
 int srt_resolve_sum(srt_backend *b, uint32_t total_samples) {
     if (!b) return SRT_ERR_INVALID;
     if (!b->d_accum || total_samples == 0) return fail(b, SRT_ERR_INVALID, "srt_resolve_sum: no image or zero samples");
@@ -1555,9 +1592,8 @@ int srt_resolve_sum(srt_backend *b, uint32_t total_samples) {
     const uint32_t n = b->width * b->height;
     const volatile float one = 1.0f;
     const float inv_n = one / (float)total_samples;
-    static const int variant = getenv("SRT_RESOLVE_VARIANT") ? atoi(getenv("SRT_RESOLVE_VARIANT")) : 0;
     // the 8-byte RGBA8 store of the two-pixel kernel needs an 8-byte aligned image (cudaMalloc / torch buffers are)
-    if (variant == 1 || (reinterpret_cast<uintptr_t>(b->d_rgba) & 7u) != 0)
+    if (b->knobs.resolve_variant == 1 || (reinterpret_cast<uintptr_t>(b->d_rgba) & 7u) != 0)
         resolve_sum_kernel_1px<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->d_rgba, n, inv_n);
     else
         resolve_sum_kernel<<<((n + 1) / 2 + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->d_rgba, n, inv_n);
@@ -1571,7 +1607,8 @@ int srt_read_rgba8(srt_backend *b, void *dst) {
     if (!b || !dst) return SRT_ERR_INVALID;
     if (!b->d_rgba) return fail(b, SRT_ERR_INVALID, "srt_read_rgba8: no image");
     SRT_CUDA(b, cudaSetDevice(b->device));
-    SRT_CUDA(b, cudaMemcpyAsync(dst, b->d_rgba, (size_t)b->width * b->height * 4, cudaMemcpyDeviceToHost, b->stream));
+    const uint32_t *src = b->gathered_rgba ? b->d_gather_rgba : b->d_rgba;   // after srt_gather_rgba: the combined image
+    SRT_CUDA(b, cudaMemcpyAsync(dst, src, (size_t)b->width * b->height * 4, cudaMemcpyDeviceToHost, b->stream));
     SRT_CUDA(b, cudaStreamSynchronize(b->stream));
     b->in_flight = false;
     return SRT_OK;
@@ -1581,7 +1618,8 @@ int srt_read_accum(srt_backend *b, float *dst) {
     if (!b || !dst) return SRT_ERR_INVALID;
     if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_read_accum: no image");
     SRT_CUDA(b, cudaSetDevice(b->device));
-    SRT_CUDA(b, cudaMemcpyAsync(dst, b->d_accum, (size_t)b->width * b->height * 16, cudaMemcpyDeviceToHost, b->stream));
+    const float4 *src = b->gathered_accum ? b->d_gather_accum : b->d_accum;
+    SRT_CUDA(b, cudaMemcpyAsync(dst, src, (size_t)b->width * b->height * 16, cudaMemcpyDeviceToHost, b->stream));
     SRT_CUDA(b, cudaStreamSynchronize(b->stream));
     b->in_flight = false;
     return SRT_OK;
@@ -1592,6 +1630,11 @@ int srt_write_accum(srt_backend *b, const float *src) {
     if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_write_accum: no image (call srt_resize)");
     SRT_CUDA(b, cudaSetDevice(b->device));
     SRT_CUDA(b, cudaMemcpyAsync(b->d_accum, src, (size_t)b->width * b->height * 16, cudaMemcpyHostToDevice, b->stream));
+    if (b->n_parts > 1u) {   // image partition: rows of other devices must stay zero (the combine step is a sum)
+        const uint32_t n = b->width * b->height;
+        clear_foreign_rows<<<(n + 255) / 256, 256, 0, b->stream>>>(b->d_accum, b->width, n, b->part, b->n_parts);
+        SRT_CUDA(b, cudaGetLastError());
+    }
     SRT_CUDA(b, cudaStreamSynchronize(b->stream));
     b->in_flight = false;
     return SRT_OK;
@@ -1612,6 +1655,130 @@ int srt_read_primary(srt_backend *b, uint32_t *prim, float *t) {
 void *srt_accum_device_ptr(srt_backend *b) { return b ? (void *)b->d_accum : nullptr; }
 void *srt_rgba_device_ptr(srt_backend *b) { return b ? (void *)b->d_rgba : nullptr; }
 void *srt_cuda_stream(srt_backend *b) { return b ? (void *)b->stream : nullptr; }
+
+// ---- multi-device: one handle per device, one host thread or process per handle ----------------------------
+// The reference fans a frame out to ThreadCount workers (WorkQueueStart, base.h:174, main.cpp:851-856) that pull
+// 32x32 tiles (main.cpp:9, 362-368); here the workers are GPUs and the one exchange step is an NCCL reduce on the
+// handle's stream.
+int srt_comm_unique_id(void *id_out) {
+    if (!id_out) return fail(nullptr, SRT_ERR_INVALID, "srt_comm_unique_id: null output");
+    NcclApi &N = nccl_api();
+    if (!N.GetUniqueId) return fail(nullptr, SRT_ERR_COMM, "srt_comm_unique_id: " + N.error);
+    static_assert(sizeof(ncclUniqueId) == SRT_COMM_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId id;
+    const ncclResult_t r = N.GetUniqueId(&id);
+    if (r != ncclSuccess) return fail(nullptr, SRT_ERR_COMM, std::string("ncclGetUniqueId: ") + N.GetErrorString(r));
+    memcpy(id_out, &id, sizeof(id));
+    return SRT_OK;
+}
+
+// One host thread that drives several handles brackets each round of collective calls (and the init calls): NCCL
+// then treats them as one operation instead of blocking in the first.
+int srt_comm_group_begin(void) {
+    NcclApi &N = nccl_api();
+    if (!N.GroupStart) return fail(nullptr, SRT_ERR_COMM, "srt_comm_group_begin: " + N.error);
+    const ncclResult_t r = N.GroupStart();
+    return r == ncclSuccess ? SRT_OK : fail(nullptr, SRT_ERR_COMM, std::string("ncclGroupStart: ") + N.GetErrorString(r));
+}
+int srt_comm_group_end(void) {
+    NcclApi &N = nccl_api();
+    if (!N.GroupEnd) return fail(nullptr, SRT_ERR_COMM, "srt_comm_group_end: " + N.error);
+    const ncclResult_t r = N.GroupEnd();
+    return r == ncclSuccess ? SRT_OK : fail(nullptr, SRT_ERR_COMM, std::string("ncclGroupEnd: ") + N.GetErrorString(r));
+}
+
+int srt_comm_init_rank(srt_backend *b, int n_ranks, int rank, const void *unique_id) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!unique_id || n_ranks < 1 || rank < 0 || rank >= n_ranks) return fail(b, SRT_ERR_INVALID, "srt_comm_init_rank: bad rank / n_ranks / id");
+    NcclApi &N = nccl_api();
+    if (!N.CommInitRank || !N.Reduce || !N.AllReduce || !N.CommDestroy) return fail(b, SRT_ERR_COMM, "srt_comm_init_rank: " + (N.error.empty() ? std::string("NCCL unavailable") : N.error));
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    int rc = drain(b);
+    if (rc) return rc;
+    comm_release(b);
+    ncclUniqueId id;
+    memcpy(&id, unique_id, sizeof(id));
+    ncclComm_t comm = nullptr;
+    SRT_NCCL(b, N.CommInitRank(&comm, n_ranks, id, rank));
+    b->comm = comm;
+    b->comm_rank = rank;
+    b->comm_size = n_ranks;
+    return SRT_OK;
+}
+
+int srt_comm_destroy(srt_backend *b) {
+    if (!b) return SRT_ERR_INVALID;
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    int rc = drain(b);
+    if (rc) return rc;
+    comm_release(b);
+    return SRT_OK;
+}
+
+int srt_comm_info(srt_backend *b, int *rank, int *n_ranks, int *nccl_version) {
+    if (!b) return SRT_ERR_INVALID;
+    if (rank) *rank = b->comm_rank;
+    if (n_ranks) *n_ranks = b->comm ? b->comm_size : 0;
+    if (nccl_version) { *nccl_version = 0; NcclApi &N = nccl_api(); if (N.GetVersion) N.GetVersion(nccl_version); }
+    return SRT_OK;
+}
+
+int srt_set_partition(srt_backend *b, uint32_t part, uint32_t n_parts) {
+    if (!b) return SRT_ERR_INVALID;
+    if (n_parts == 0 || part >= n_parts || n_parts > 65535u) return fail(b, SRT_ERR_INVALID, "srt_set_partition: need part < n_parts <= 65535");
+    int rc = drain(b);
+    if (rc) return rc;
+    const bool changed = part != b->part || n_parts != b->n_parts;
+    b->part = part;
+    b->n_parts = n_parts;
+    // rows that now belong to another device must read as zero: the combine step is a sum
+    return (changed && b->d_accum) ? srt_reset_accumulation(b) : SRT_OK;
+}
+
+// Sample sharding: every device holds a SUM over its samples of every pixel (SRT_ACCUM_SUM).
+int srt_reduce_accum(srt_backend *b, int root) {
+    if (!b) return SRT_ERR_INVALID;
+    if (!b->comm) return fail(b, SRT_ERR_INVALID, "srt_reduce_accum: no communicator (call srt_comm_init_rank)");
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, "srt_reduce_accum: no image");
+    if (root >= b->comm_size) return fail(b, SRT_ERR_INVALID, "srt_reduce_accum: bad root");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    NcclApi &N = nccl_api();
+    const size_t n = (size_t)b->width * b->height * 4;
+    if (root < 0) SRT_NCCL(b, N.AllReduce(b->d_accum, b->d_accum, n, ncclFloat32, ncclSum, (ncclComm_t)b->comm, b->stream));
+    else SRT_NCCL(b, N.Reduce(b->d_accum, b->d_accum, n, ncclFloat32, ncclSum, root, (ncclComm_t)b->comm, b->stream));
+    b->launches += 1;
+    b->in_flight = true;
+    return SRT_OK;
+}
+
+// Image partition: the rows a device does not own are zero in its buffers, so an integer (RGBA8 words) or f32
+// (x + 0 = x) sum over the devices IS the gather of the row bands -- bit-identical to a single-device render.
+static int gather_image(srt_backend *b, int root, bool accum, const char *who) {
+    const std::string w(who);
+    if (!b->comm) return fail(b, SRT_ERR_INVALID, w + ": no communicator (call srt_comm_init_rank)");
+    if (!b->d_accum) return fail(b, SRT_ERR_INVALID, w + ": no image");
+    if (root >= b->comm_size) return fail(b, SRT_ERR_INVALID, w + ": bad root");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    NcclApi &N = nccl_api();
+    const size_t px = (size_t)b->width * b->height;
+    const bool recv = root < 0 || root == b->comm_rank;
+    void *dst = nullptr;
+    if (recv) {
+        if (accum) { if (!b->d_gather_accum) SRT_CUDA(b, cudaMalloc(&b->d_gather_accum, px * sizeof(float4))); dst = b->d_gather_accum; }
+        else { if (!b->d_gather_rgba) SRT_CUDA(b, cudaMalloc(&b->d_gather_rgba, px * sizeof(uint32_t))); dst = b->d_gather_rgba; }
+    }
+    const void *src = accum ? (const void *)b->d_accum : (const void *)b->d_rgba;
+    const size_t n = accum ? px * 4 : px;
+    const ncclDataType_t ty = accum ? ncclFloat32 : ncclUint32;
+    if (root < 0) SRT_NCCL(b, N.AllReduce(src, dst, n, ty, ncclSum, (ncclComm_t)b->comm, b->stream));
+    else SRT_NCCL(b, N.Reduce(src, recv ? dst : (void *)src, n, ty, ncclSum, root, (ncclComm_t)b->comm, b->stream));
+    if (recv) { if (accum) b->gathered_accum = true; else b->gathered_rgba = true; }
+    b->launches += 1;
+    b->in_flight = true;
+    return SRT_OK;
+}
+int srt_gather_rgba(srt_backend *b, int root) { return b ? gather_image(b, root, false, "srt_gather_rgba") : SRT_ERR_INVALID; }
+int srt_gather_accum(srt_backend *b, int root) { return b ? gather_image(b, root, true, "srt_gather_accum") : SRT_ERR_INVALID; }
 
 int srt_device_info(srt_backend *b, int *sm_count, int *clock_khz, uint64_t *launches) {
     if (!b) return SRT_ERR_INVALID;

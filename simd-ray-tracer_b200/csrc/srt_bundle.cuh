@@ -81,7 +81,7 @@ __device__ __forceinline__ void bundle_scan(const float4 *__restrict__ tab, uint
     for (uint32_t g0 = first >> 2; g0 < g_end; g0 += 32u) {
         const uint32_t grp = g0 + lane;
         const bool in = grp < g_end;
-        float4 Pp = make_float4(0.f, 0.f, 0.f, 0.f), Qq = Pp, Rr = make_float4(-1.f, -1.f, -1.f, -1.f);
+        float4 Pp = make_float4(0.f, 0.f, 0.f, 0.f), Qq = Pp, Rr = make_float4(-1.0e30f, -1.0e30f, -1.0e30f, -1.0e30f);
         if (in) {
             const float4 *g = tab + 3u * grp;
             if (GLOBAL) { Pp = __ldg(g); Qq = __ldg(g + 1); Rr = __ldg(g + 2); }
@@ -105,6 +105,9 @@ __device__ __forceinline__ void bundle_scan(const float4 *__restrict__ tab, uint
                 if (bundle_test(Pp.w, Qq.w, Rr.w, op, oq, b)) nib |= 1u;
             }
         }
+        // Lanes past the end of the table (n_pad % 128 != 0) ran the test on {0, 0, -1}: |nou| <= wl * eps - 1 CAN hold for a
+        // far camera and a coarse image (eps ~ 0.05, |O| ~ 1e2), and a set bit would name a sphere index >= n_pad.
+        if (!in) nib = 0u;
         uint32_t word = nib << (28u - 4u * (lane & 7u));          // bit 31 - j = sphere j of the 32-sphere chunk
         word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
         word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);

@@ -20,6 +20,24 @@ constexpr int kMaxBounce = 5;   // MaxRayBounce main.cpp:387
 
 struct f3 { float x, y, z; };
 
+// Debug build (-DSRT_SPIN_LIMIT=N): every wait loop of the pool kernel -- ring pop / push, batch acquisition, the
+// TMA stage barrier -- reports its site to pinned host memory and traps after N iterations, so that a protocol bug
+// reads as "spin limit at site s" from srt_wait instead of a hung GPU (compute-sanitizer is not available on the pool).
+enum : uint32_t { kSpinPop = 1, kSpinPush = 2, kSpinAcquire = 3, kSpinMbar = 4 };
+#ifdef SRT_SPIN_LIMIT
+__device__ unsigned long long *g_spin_report;     // pinned + mapped host word of the handle that launched last
+__device__ __noinline__ void spin_fail(uint32_t site) {
+    if (g_spin_report) {
+        *(volatile unsigned long long *)g_spin_report = 0xDEAD000000000000ull | ((unsigned long long)site << 32) | (blockIdx.x << 12) | (threadIdx.x & 0xFFFu);
+        __threadfence_system();
+    }
+    __trap();
+}
+#define SRT_SPIN(site, n) do { if (++(n) > (uint32_t)(SRT_SPIN_LIMIT)) spin_fail(site); } while (0)
+#else
+#define SRT_SPIN(site, n) do { (void)(n); } while (0)
+#endif
+
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
 __device__ __forceinline__ f3 add3(f3 a, f3 b) { return mk3(__fadd_rn(a.x, b.x), __fadd_rn(a.y, b.y), __fadd_rn(a.z, b.z)); }
 __device__ __forceinline__ f3 sub3(f3 a, f3 b) { return mk3(__fsub_rn(a.x, b.x), __fsub_rn(a.y, b.y), __fsub_rn(a.z, b.z)); }
@@ -145,6 +163,9 @@ struct KernelParams {
     float *tap_t;                // optional
     unsigned long long *rays;
     unsigned int *work_counter;
+    unsigned int *ticket;        // CTAs that have left the launch; the last one publishes *rays to *host_rays and re-arms the counters
+    unsigned long long *host_rays;   // pinned + mapped host memory: path segments cast by the launch (main.cpp:390)
+    uint32_t part, n_parts;      // image partition over devices (srt_set_partition): local block row L is block row L * n_parts + part
     unsigned long long *debug;   // optional diagnostics (pool kernel)
     // pool kernel work items: (sample chunk, pixel), chunk-major, so that the end of a launch does not
     // wait for single pixels to run all their samples

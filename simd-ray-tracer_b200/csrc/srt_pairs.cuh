@@ -152,98 +152,6 @@ __device__ __forceinline__ ScanRays make_scan_rays(pk2 ox, pk2 oy, pk2 oz, pk2 d
     r.ooa = fa.oo; r.oob = fb.oo;
     return r;
 }
-//   tile : shared memory, count x {cx, cy, cz, -kappa} (padding: -kappa = -1e30, never a candidate)
-template <int SUB>
-__device__ __forceinline__ void scan_general_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first,
-                                                  const ScanRays &r, CandQueue &queue, uint32_t &qn) {
-    const uint32_t full = count >> 5;
-#pragma unroll 1
-    for (uint32_t c = 0; c < full; ++c) {
-        uint32_t mask = 0;
-#pragma unroll 1
-        for (int sub = 0; sub < 32 / SUB; ++sub) {
-            const float4 *blk = tile + (c << 5) + sub * SUB;
-            uint32_t m = 0;
-#pragma unroll
-            for (int j = 0; j < SUB; ++j) filter_sphere(m, (1u << (SUB - 1)) >> j, blk[j], r.p2ox, r.p2oy, r.p2oz, r.dx, r.dy, r.dz, r.od, r.ooa, r.oob);
-            mask = SUB == 32 ? m : ((mask << (SUB & 31)) | m);
-        }
-        if (mask) { queue[qn] = make_uint2(mask, first + (c << 5)); qn += 1; }
-    }
-    if (count & 31u) {                       // tail: 1..3 blocks of 8
-        uint32_t mask = 0, cnt = 0;
-#pragma unroll 1
-        for (uint32_t base = full << 5; base < count; base += 8, cnt += 8) {
-            uint32_t m = 0;
-#pragma unroll
-            for (int j = 0; j < 8; ++j) filter_sphere(m, 0x80u >> j, tile[base + j], r.p2ox, r.p2oy, r.p2oz, r.dx, r.dy, r.dz, r.od, r.ooa, r.oob);
-            mask = (mask << 8) | m;
-        }
-        mask <<= (32u - cnt);                // cnt in {8,16,24}: first tail sphere -> bit 31
-        if (mask) { queue[qn] = make_uint2(mask, first + (full << 5)); qn += 1; }
-    }
-}
-
-// PRIMARY rays: every ray of the launch starts at the camera position O, so
-// 2 C.O - kappa - oo' is a per-sphere constant (`ptab[i].w`, evaluated in double per launch) and
-// the candidate test becomes  z = tt^2 + ptab.w > 0 :  4 FFMA2 + LDS.128 + LOP3 + SHF per sphere
-// per 64 rays (the sign bits of the two halves are AND-ed and shifted into the mask, which is
-// inverted per chunk).
-struct ScanPrimary { pk2 dx, dy, dz, od; };
-__device__ __forceinline__ ScanPrimary make_scan_primary(float ox, float oy, float oz, pk2 dx, pk2 dy, pk2 dz) {
-    float dxa, dxb, dya, dyb, dza, dzb;
-    pk_split(dx, dxa, dxb); pk_split(dy, dya, dyb); pk_split(dz, dza, dzb);
-    const FilterRay fa = filter_ray(ox, oy, oz, dxa, dya, dza), fb = filter_ray(ox, oy, oz, dxb, dyb, dzb);
-    ScanPrimary r;
-    r.dx = pk_make(fa.dx, fb.dx); r.dy = pk_make(fa.dy, fb.dy); r.dz = pk_make(fa.dz, fb.dz);
-    r.od = pk_make(fa.od, fb.od);
-    return r;
-}
-__device__ __forceinline__ void primary_sphere(uint32_t &nmask, const float4 s, pk2 dx, pk2 dy, pk2 dz, pk2 od) {
-    const pk2 cx = pk_make(s.x, s.x), cy = pk_make(s.y, s.y), cz = pk_make(s.z, s.z);
-    const pk2 tt = pk_fma(cx, dx, pk_fma(cy, dy, pk_fma(cz, dz, od)));
-    const pk2 z = pk_fma(tt, tt, pk_make(s.w, s.w));
-    float za, zb;
-    pk_split(z, za, zb);
-    nmask = __funnelshift_l(__float_as_uint(za) & __float_as_uint(zb), nmask, 1);   // 1 = both rays miss for sure
-}
-template <int SUB>
-__device__ __forceinline__ void scan_primary_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first,
-                                                  const ScanPrimary &r, CandQueue &queue, uint32_t &qn) {
-    const uint32_t full = count >> 5;
-#pragma unroll 1
-    for (uint32_t c = 0; c < full; ++c) {
-        uint32_t nmask = 0;
-#pragma unroll 1
-        for (int sub = 0; sub < 32 / SUB; ++sub) {
-            const float4 *blk = tile + (c << 5) + sub * SUB;
-#pragma unroll
-            for (int j = 0; j < SUB; ++j) primary_sphere(nmask, blk[j], r.dx, r.dy, r.dz, r.od);
-        }
-        if (~nmask) { queue[qn] = make_uint2(~nmask, first + (c << 5)); qn += 1; }
-    }
-    if (count & 31u) {
-        uint32_t nmask = 0, cnt = 0;
-#pragma unroll 1
-        for (uint32_t base = full << 5; base < count; base += 8, cnt += 8) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) primary_sphere(nmask, tile[base + j], r.dx, r.dy, r.dz, r.od);
-        }
-        const uint32_t mask = (~nmask) << (32u - cnt);          // cnt in {8,16,24}: first tail sphere -> bit 31
-        if (mask) { queue[qn] = make_uint2(mask, first + (full << 5)); qn += 1; }
-    }
-}
-
-// Overloads by ray-constant type, for code that is generic over the kind of pass.
-template <int SUB>
-__device__ __forceinline__ void scan_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first, const ScanRays &r, CandQueue &queue, uint32_t &qn) {
-    scan_general_tile<SUB>(tile, count, first, r, queue, qn);
-}
-template <int SUB>
-__device__ __forceinline__ void scan_tile(const float4 *__restrict__ tile, uint32_t count, uint32_t first, const ScanPrimary &r, CandQueue &queue, uint32_t &qn) {
-    scan_primary_tile<SUB>(tile, count, first, r, queue, qn);
-}
-
 // ---- level 1: slab scan -- 2 packed FMAs + 2 compares + 1 mask update per sphere per ray pair -----
 // A sphere the ray hits lies within its radius of the ray's LINE, hence within its radius of any
 // plane that contains the line.  Take the plane spanned by the ray and one fixed coordinate axis
@@ -259,7 +167,9 @@ __device__ __forceinline__ void scan_tile(const float4 *__restrict__ tile, uint3
 // <= 7.4u(|C|+|O|) in total.  r' = r(1+32u) + 32u(|C| + Omax) + 1e-30 covers both as long as
 // |O| <= Omax (the launch's bound on ray origins); a ray with a larger origin, a near-axis
 // direction (|(D_p, D_q)|^2 < 1e-16) or a NaN takes U = 0, O.U = 0: every sphere is a candidate.
-// Parked halves (O = kIdleOrigin) take -O.U = -inf: no candidates.  Padding has r' = -1.
+// Parked halves (O = kIdleOrigin) take -O.U = -inf: no candidates.  Padding has r' = -1e30 (kSlabPadRadius): the
+// level-0 bound r' + wl * eps of srt_bundle.cuh stays negative for it whatever the camera.
+constexpr float kSlabPadRadius = -1.0e30f;
 struct SlabRay { float up, uq, nou; };
 __device__ __forceinline__ SlabRay slab_ray(int axis, float ox, float oy, float oz, float dx, float dy, float dz, float omax2) {
     const float op = axis == 0 ? oy : (axis == 1 ? oz : ox), oq = axis == 0 ? oz : (axis == 1 ? ox : oy);
@@ -443,22 +353,6 @@ __device__ __forceinline__ void select_finish(const float4 *__restrict__ sph_glo
             if (amb1) h1.inside = replay_inside<W, FMA>(sph_global, n_pad, oxb, oyb, ozb, dxb, dyb, dzb) != 0;
         }
     }
-}
-
-// Scan + select (general rays, resident tables) for the two rays of a thread.
-template <int W, bool FMA>
-__device__ __forceinline__ void intersect_pair(const float4 *__restrict__ scan, const float *__restrict__ r2tab,
-                                               const float4 *__restrict__ sph_global, uint32_t n_pad, uint32_t n_real,
-                                               pk2 ox, pk2 oy, pk2 oz, pk2 dx, pk2 dy, pk2 dz,
-                                               float neg_one_f, float one_f, Hit &h0, Hit &h1) {
-    CandQueue queue;
-    uint32_t qn = 0;
-    const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
-    scan_general_tile<32>(scan, n_pad, 0u, rays, queue, qn);
-    Best b0 = best_init(), b1 = best_init();
-    const FetchResident fetch = {scan, r2tab};
-    select_update<W, FMA>(fetch, n_real, queue, qn, ox, oy, oz, dx, dy, dz, neg_one_f, one_f, b0, b1);
-    select_finish<W, FMA>(sph_global, n_pad, b0, b1, ox, oy, oz, dx, dy, dz, h0, h1);
 }
 
 } // namespace srt

@@ -11,12 +11,35 @@ constexpr uint32_t kInvalidPixel = 0xFFFFFFFFu;
 // Work item i -> pixel: 8x4 pixel blocks, row-major over blocks, so that a fresh warp
 // covers a compact screen patch (coherent primary rays: the rare hit branch and the
 // material branch diverge less).  Returns false for items outside the image.
+// Image partition (multi-device, srt_set_partition): a handle renders every n_parts-th row of blocks -- the
+// reference hands 32x32 tiles to its worker threads (main.cpp:9, 362-368, 824-827); here the unit is a row of
+// 8x4 blocks, interleaved so that sky rows and ground rows spread evenly over the devices.
 __device__ __forceinline__ bool item_to_pixel(const KernelParams &P, uint32_t item, uint32_t &px, uint32_t &py) {
     const uint32_t blk = item >> 5, in = item & 31u;
     const uint32_t by = magic_div(blk, P.div_bx), bx = blk - by * P.blocks_x;
     px = bx * 8u + (in & 7u);
-    py = by * 4u + (in >> 3);
+    py = (by * P.n_parts + P.part) * 4u + (in >> 3);
     return px < P.width && py < P.height;
+}
+
+// Launch epilogue of every render kernel: the warp's ray count (main.cpp:390) joins the launch total; the LAST CTA
+// to leave publishes the total to pinned host memory and re-arms the launch counters, so a frame costs the host one
+// kernel launch -- no memset, no copy (the kick replaces WorkQueueStart, main.cpp:852).  All threads must call it.
+__device__ __forceinline__ void finish_launch(const KernelParams &P, unsigned long long rays) {
+    for (int off = 16; off > 0; off >>= 1) rays += __shfl_down_sync(0xFFFFFFFFu, rays, off);
+    if ((threadIdx.x & 31u) == 0 && rays) atomicAdd(P.rays, rays);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(P.ticket, 1u) == gridDim.x - 1u) {
+            __threadfence();
+            const unsigned long long total = atomicExch(P.rays, 0ull);
+            *P.work_counter = 0u;
+            *P.ticket = 0u;
+            *(volatile unsigned long long *)P.host_rays = total;
+            __threadfence_system();
+        }
+    }
 }
 
 // A1 primary ray, main.cpp:375-385.  Stream contract: the path (sample k,

@@ -1,16 +1,15 @@
-// srt_pool.cuh -- CTA-level path pools for the ray-pair kernel (sm_100a).
+// srt_pool.cuh -- CTA-level path pools of the pool kernel (sm_100a).
 //
-// render_pairs binds two path slots to a thread, so every pass mixes primary rays (fresh
-// samples) with secondary rays.  Primary rays all start at the camera: their filter needs
-// 4 FFMA2 per sphere instead of 7 (scan_primary, srt_pairs.cuh) -- but only if a whole warp
-// pass consists of primaries.  Here the path slots therefore belong to the CTA, not to a
-// thread: two rings in shared memory hold the ids of the slots that need a NEW PRIMARY ray
-// (ring P) and of those with a SECONDARY ray ready (ring S), and a warp repeatedly takes 64
-// ids of one kind, runs regenerate / scan / select / shade on them (two per lane, packed in
-// the f32x2 halves) and pushes every slot back to the ring its next step needs
-// (warp-aggregated, ballot + popc).  A slot still owns its pixel for all samples of the
-// launch, one path in flight per pixel, so the running mean of main.cpp:484-489 keeps its
-// order and every buffer stays bit-identical.
+// A thread that owns its two path slots mixes fresh primary rays with secondary rays in every
+// pass, and regeneration runs for a fraction of the lanes each time.  Here the path slots belong
+// to the CTA, not to a thread: rings in shared memory hold the ids of the slots that need a
+// NEW PRIMARY ray (ring P), of those with a SECONDARY ray ready (ring S) and -- bundle mode --
+// of those that delivered the last sample of a pixel chunk and must fold it (ring F).  A warp
+// repeatedly takes 64 ids of one kind, runs regenerate / scan / select / shade on them (two per
+// lane, packed in the f32x2 halves) and pushes every slot back to the ring its next step needs
+// (warp-aggregated, ballot + popc).  Work items are (sample chunk, pixel) pairs handed out by a
+// global counter; a pixel's chunks fold in order through done[pix] (srt_backend.cu), so the
+// running mean of main.cpp:484-489 keeps its order and every buffer stays bit-identical.
 //
 // Ring protocol (multi-producer / multi-consumer, no CTA barrier after start-up):
 //   push: pos = atomicAdd(tail, n); wait until ring[pos+i] is EMPTY; write id; fence;
@@ -75,6 +74,7 @@ __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, boo
         if (FOLD && pool_try_take(ctl, 2, 1u, n, pos)) { kind = 2; return; }   // the chunk being waited for may sit in ring F
         if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
     }
+    [[maybe_unused]] uint32_t spins = 0;
     for (;;) {
         if (FOLD && pool_try_take(ctl, 2, kFoldBatchMin, n, pos)) { kind = 2; return; }  // enough chunks to fold, one per lane
         if (pool_try_take(ctl, 0, 64u, n, pos)) { kind = 0; return; }
@@ -87,13 +87,15 @@ __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, boo
         }
         if (*(volatile unsigned int *)&ctl->retired) ctl->spins_tail += 1; else ctl->spins_steady += 1;   // racy, diagnostic only
         __nanosleep(100);
+        SRT_SPIN(kSpinAcquire, spins);
     }
 }
 
 __device__ __forceinline__ uint32_t pool_pop(ring_t *ring, uint32_t cap_mask, uint32_t pos) {
     volatile ring_t *e = ring + (pos & cap_mask);
     ring_t id;
-    while ((id = *e) == kRingSlotEmpty) { }
+    [[maybe_unused]] uint32_t spins = 0;
+    while ((id = *e) == kRingSlotEmpty) { SRT_SPIN(kSpinPop, spins); }
     *e = kRingSlotEmpty;
     return id;
 }
@@ -108,7 +110,8 @@ __device__ __forceinline__ void pool_push(PoolCtl *ctl, ring_t *ring, uint32_t c
     pos = __shfl_sync(0xFFFFFFFFu, pos, leader);
     if (doit) {
         volatile ring_t *e = ring + ((pos + __popc(m & ((1u << lane) - 1u))) & cap_mask);
-        while (*e != kRingSlotEmpty) { }
+        [[maybe_unused]] uint32_t spins = 0;
+        while (*e != kRingSlotEmpty) { SRT_SPIN(kSpinPush, spins); }
         *e = (ring_t)id;
     }
     __threadfence_block();

@@ -11,6 +11,7 @@
 // first pass.
 #pragma once
 #include <stdint.h>
+#include "srt_device.cuh"
 
 namespace srt {
 
@@ -38,8 +39,19 @@ __device__ __forceinline__ void stream_issue(void *dst, const void *src, uint32_
                  ::"r"(smem_addr(dst)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+#ifdef SRT_SPIN_LIMIT
+    uint32_t spins = 0;
+    for (;;) {
+        uint32_t ok;
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+        if (ok) break;
+        SRT_SPIN(kSpinMbar, spins);
+    }
+#else
     asm volatile("{\n\t.reg .pred p;\n\tWAIT_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}"
                  ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+#endif
 }
 
 // Per-warp stream state: the ring of stages and the parity each stage's barrier will show next.

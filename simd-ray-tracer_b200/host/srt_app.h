@@ -43,13 +43,16 @@ struct image { void *Data; u32 Width, Height; format Format; };
 
 struct init_params { u32 WindowWidth, WindowHeight; const char *WindowTitle; };
 
-// render_params base.h:157-161.  ThreadCount is meaningless on the GPU and ignored;
+// render_params base.h:157-161.  ThreadCount = workers used for the frame (WorkQueueStart(.., ThreadCount),
+// main.cpp:851-856): here the workers are the GPUs OnInit created; 0 or too many = all of them.
 // EnableSIMD picks RenderTile (lanes) vs RenderTileScalar semantics as in main.cpp:852-856.
 struct render_params { u32 ThreadCount; bool EnableSIMD; u32 SceneIndex; };
 
 // Backend knobs that have no counterpart in the reference (set before OnInit).
+constexpr u32 MaxDeviceCount = 16;
 struct backend_params {
-    int DeviceId = 0;
+    int DeviceId = 0;         // first CUDA ordinal
+    u32 DeviceCount = 1;      // GPUs DeviceId .. DeviceId + DeviceCount - 1 become the frame's workers (WorkQueueCreate, main.cpp:660)
     u32 LaneWidth = 8;        // SIMD_WIDTH the lanes emulate (base.h:53-64): 8 (AVX2) or 4 (SSE/wasm)
     bool FmaDot = true;       // x64_math.h:409-420 (AVX2 profile) vs 299-309
     u32 SamplesPerFrame = 1;  // the reference renders exactly 1 spp per frame (main.cpp:484)
@@ -76,13 +79,19 @@ const char *LastError();
 const scene *GetScene(u32 SceneIndex);
 u32 GetAccumulatedSampleCount();                       // PreviousRayCount + completed frame
 void WaitForFrame();                                   // WorkQueueWaitUntilCompletion
+// Publish the frame in flight without kicking another one (end of a batch render): waits, gathers the workers'
+// rows, copies the RGBA8 image to Image.Data (if any) and returns the frame's statistics.
+bool PublishFrame(const image &Image, u64 *OutTotalRaysCast, f64 *OutTimeElapsed);
+u32 GetDeviceCount();
 bool ReadAccumulator(f32 *Dst);                        // PreviousImage, W*H*4 floats
 srt_backend *GetBackend();
 void ComputeCamera(const scene &Scene, f32 Distance, f32 XAngle, f32 YHeight, u32 Width, u32 Height, srt_camera *Out);
 
 // Files either side of the path (srt_files.cpp): accumulator checkpoints and scene descriptions.
 #include <vector>
-struct checkpoint_header { u32 Width, Height, Samples, SceneIndex; u64 StreamBase; u32 LaneWidth, FmaDot; };
+struct checkpoint_header { u32 Width, Height, Samples, SceneIndex; u64 StreamBase; u32 LaneWidth, FmaDot; u64 SceneHash; };   // SceneHash 0: unknown
+u64 HashScene(const scene &Scene);                      // FNV-1a of the sphere table + sky flag
+u32 GetSceneGeneration(u32 SceneIndex);                 // bumped by SetScene / ResetScene
 bool SaveCheckpoint(const char *Path, const checkpoint_header &Header, const f32 *Accum);
 bool LoadCheckpoint(const char *Path, checkpoint_header *Header, std::vector<f32> *Accum);
 bool SaveSceneFile(const char *Path, const scene &Scene);

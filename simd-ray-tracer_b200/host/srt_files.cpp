@@ -4,9 +4,11 @@
 // accumulator lives in an arena (main.cpp:801-804).  These two formats make long renders
 // restartable and let scenes beyond the five built-in ones reach srt_set_scene:
 //
-//   checkpoint (binary, little endian):  "SRTCKPT1" | u32 width | u32 height | u32 samples |
-//       u32 scene_index | u64 stream_base | u32 lane_width | u32 fma_dot | f32 accum[W*H*4]
+//   checkpoint (binary, little endian):  "SRTCKPT2" | u32 width | u32 height | u32 samples |
+//       u32 scene_index | u64 stream_base | u32 lane_width | u32 fma_dot | u64 scene_hash | f32 accum[W*H*4]
 //       `samples` = PreviousRayCount (main.cpp:7): the next frame renders sample index `samples`.
+//       lane_width / fma_dot / scene_hash pin the arithmetic profile and the sphere table the samples were
+//       rendered with: a resume under anything else would silently break the bit-identical guarantee.
 //
 //   scene (text, one record per line, '#' comments; %.9g round-trips every f32 exactly):
 //       sky 0|1
@@ -20,7 +22,7 @@
 #include <string.h>
 #include <vector>
 
-static const char kMagic[8] = {'S', 'R', 'T', 'C', 'K', 'P', 'T', '1'};
+static const char kMagic[8] = {'S', 'R', 'T', 'C', 'K', 'P', 'T', '2'};
 
 bool SaveCheckpoint(const char *Path, const checkpoint_header &Header, const f32 *Accum) {
     FILE *F = fopen(Path, "wb");
@@ -38,11 +40,16 @@ bool LoadCheckpoint(const char *Path, checkpoint_header *Header, std::vector<f32
     bool Ok = fread(Magic, 1, 8, F) == 8 && memcmp(Magic, kMagic, 8) == 0 && fread(Header, sizeof(*Header), 1, F) == 1;
     if (Ok && (Header->Width == 0 || Header->Height == 0 || (u64)Header->Width * Header->Height > 0x7FFFFFFFull)) Ok = false;
     if (Ok) {
+        // the payload length must match the header BEFORE anything is allocated (a damaged header could ask for 32 GiB)
         const size_t N = (size_t)Header->Width * Header->Height * 4;
-        Accum->resize(N);
-        Ok = fread(Accum->data(), sizeof(f32), N, F) == N;
-        char Extra;
-        if (Ok && fread(&Extra, 1, 1, F) != 0) Ok = false;      // trailing bytes: not one of ours
+        const long Here = ftell(F);
+        Ok = Here >= 0 && fseek(F, 0, SEEK_END) == 0;
+        const long End = Ok ? ftell(F) : -1;
+        Ok = Ok && End >= Here && (u64)(End - Here) == (u64)N * sizeof(f32) && fseek(F, Here, SEEK_SET) == 0;
+        if (Ok) {
+            Accum->resize(N);
+            Ok = fread(Accum->data(), sizeof(f32), N, F) == N;
+        }
     }
     fclose(F);
     return Ok;

@@ -44,14 +44,16 @@ static bool WritePfm(const char *Path, const f32 *Accum, u32 W, u32 H) {
 static void Usage() {
     fprintf(stderr,
             "usage: srt_headless [--scene 0..4] [--width W] [--height H] [--spp N] [--spf K]\n"
-            "                    [--simd 0|1] [--lanes 4|8] [--fma 0|1] [--device D] [--stream-base B]\n"
+            "                    [--simd 0|1] [--lanes 4|8] [--fma 0|1] [--device D] [--gpus N] [--stream-base B]\n"
             "                    [--orbit FRAMES] [--out image.ppm] [--accum accum.f32]\n"
             "                    [--scene-file in.scene] [--dump-scene out.scene]\n"
             "                    [--checkpoint out.ckpt] [--resume in.ckpt] [--pfm accum.pfm] [--threads N]\n"
             "  scenes: 0 RGB Glass, 1 Floating Spheres, 2 One Weekend, 3 synthetic 1,024, 4 synthetic 65,536\n"
             "  --scene-file replaces slot --scene by the file's scene; --dump-scene writes slot --scene as text.\n"
             "  --resume continues a checkpoint (same size, scene, stream base): --spp more samples are added.\n"
-            "  --pfm writes the linear accumulator as a PFM image.  --threads is render_params.ThreadCount: accepted, ignored on the GPU.\n"
+            "  --pfm writes the linear accumulator as a PFM image.\n"
+            "  --gpus N: devices D .. D+N-1 render interleaved rows of 8x4 blocks of every frame and worker 0 gathers them (NCCL);\n"
+            "  the image is bit-identical for every N.  --threads is render_params.ThreadCount: workers used per frame (0 = all).\n"
             "  --spf: samples per OnRender frame (reference: 1).  --orbit: hold key A for FRAMES frames first.\n");
 }
 
@@ -73,6 +75,7 @@ int main(int argc, char **argv) {
         else if (A == "--lanes") BP.LaneWidth = atoi(Next());
         else if (A == "--fma") BP.FmaDot = atoi(Next()) != 0;
         else if (A == "--device") BP.DeviceId = atoi(Next());
+        else if (A == "--gpus") BP.DeviceCount = atoi(Next());
         else if (A == "--stream-base") BP.StreamBase = strtoull(Next(), nullptr, 0);
         else if (A == "--orbit") Orbit = atoi(Next());
         else if (A == "--out") Out = Next();
@@ -146,19 +149,17 @@ int main(int argc, char **argv) {
         if (Published || First) { Kicked += 1; First = false; }
         else WaitForFrame();                           // not ready: block instead of spinning
     }
-    WaitForFrame();
     f64 LastMs = 0.0;
     u64 LastRays = 0;
-    srt_wait(GetBackend(), &LastMs, &LastRays);
+    if (!PublishFrame(Image, &LastRays, &LastMs)) { fprintf(stderr, "PublishFrame failed: %s\n", LastError()); return 1; }
     FrameMs.push_back(LastMs); TotalRays += LastRays; TotalMs += LastMs;
-    srt_read_rgba8(GetBackend(), Present.data());
     const f64 Wall = QueryTimestampInMilliseconds() - Wall0;
 
     if (Out && !WritePpm(Out, Present.data(), W, H)) { fprintf(stderr, "cannot write %s\n", Out); return 1; }
     if (CkptOut) {
         std::vector<f32> Acc((size_t)W * H * 4);
         ReadAccumulator(Acc.data());
-        checkpoint_header Hd = { W, H, GetAccumulatedSampleCount(), Scene, BP.StreamBase, Simd ? BP.LaneWidth : 1u, (u32)(Simd && BP.FmaDot) };
+        checkpoint_header Hd = { W, H, GetAccumulatedSampleCount(), Scene, BP.StreamBase, Simd ? BP.LaneWidth : 1u, (u32)(Simd && BP.FmaDot), HashScene(*GetScene(Scene)) };
         if (!SaveCheckpoint(CkptOut, Hd, Acc.data())) { fprintf(stderr, "cannot write %s\n", CkptOut); return 1; }
     }
     if (PfmOut) {
@@ -179,9 +180,9 @@ int main(int argc, char **argv) {
     const scene *S = GetScene(Scene);
     printf("{\"scene\": \"%s\", \"spheres\": %u, \"width\": %u, \"height\": %u, \"spp\": %u, \"frames\": %zu, "
            "\"rays\": %llu, \"device_ms\": %.4f, \"wall_ms\": %.3f, \"mrays_per_s\": %.2f, "
-           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u, \"resumed_from\": %u}\n",
+           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u, \"resumed_from\": %u, \"gpus\": %u}\n",
            S->Name, S->SphereCount, W, H, Frames * Spf, FrameMs.size(), (unsigned long long)TotalRays, TotalMs, Wall,
-           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount(), ResumedSamples);
+           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount(), ResumedSamples, GetDeviceCount());
     OnShutdown();
     return 0;
 }

@@ -42,9 +42,14 @@ int srt_host_load_scene(unsigned index, const char *path) {
 
 void srt_host_reset_scene(unsigned index) { ResetScene(index); }
 
-// Checkpoint container round trip.  header = {width, height, samples, scene_index, lane_width, fma_dot}.
+// Checkpoint container round trip.  header = {width, height, samples, scene_index, lane_width, fma_dot};
+// the scene hash is taken from slot scene_index as it is now (0 if the slot does not exist).
+unsigned long long srt_host_scene_hash(unsigned index) {
+    const scene *S = GetScene(index);
+    return S ? HashScene(*S) : 0ull;
+}
 int srt_host_save_checkpoint(const char *path, const unsigned *header, unsigned long long stream_base, const float *accum) {
-    checkpoint_header H = { header[0], header[1], header[2], header[3], stream_base, header[4], header[5] };
+    checkpoint_header H = { header[0], header[1], header[2], header[3], stream_base, header[4], header[5], srt_host_scene_hash(header[3]) };
     return SaveCheckpoint(path, H, accum) ? 0 : -1;
 }
 

@@ -230,6 +230,87 @@ void BuildSynthetic(scene *S, u32 Count, f32 BoxX, f32 BoxY, f32 BoxZ, f32 RMin,
 
 } // namespace
 
+// ---- scene registry (the reference's static Scenes[], main.cpp:53-54) and camera ------------------
+namespace {
+scene g_Scenes[SceneCount];
+bool g_SceneBuilt[SceneCount];
+u32 g_SceneGenerations[SceneCount];
+
+struct vec { f32 x, y, z; };
+vec Sub(vec a, vec b) { return { a.x - b.x, a.y - b.y, a.z - b.z }; }
+vec Cross(vec a, vec b) { return { a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x }; }
+vec Normalize(vec a) {                                                   // x64_math.h:234-245
+    const f32 L2 = (a.x * a.x + a.y * a.y) + a.z * a.z;
+    if (!(L2 > 1e-4f)) return { 0, 0, 0 };
+    const f32 L = sqrtf(L2);
+    return { a.x / L, a.y / L, a.z / L };
+}
+} // namespace
+
+const scene *GetScene(u32 SceneIndex) {
+    if (SceneIndex >= SceneCount) return nullptr;
+    if (!g_SceneBuilt[SceneIndex]) {      // the two synthetic scenes are built on first use
+        BuildScene(SceneIndex, &g_Scenes[SceneIndex]);
+        g_SceneBuilt[SceneIndex] = true;
+    }
+    return &g_Scenes[SceneIndex];
+}
+
+u32 GetSceneGeneration(u32 SceneIndex) { return SceneIndex < SceneCount ? g_SceneGenerations[SceneIndex] : 0u; }
+
+// Replace a scene slot by a caller-provided scene (copied).  A slot that is currently uploaded is
+// re-uploaded by the next OnRender (which resets the accumulation, as a scene switch does at main.cpp:718-727).
+bool SetScene(u32 SceneIndex, const scene &Scene) {
+    if (SceneIndex >= SceneCount || !Scene.ScalarSpheres || Scene.SphereCount == 0) return false;
+    scalar_sphere *Copy = (scalar_sphere *)malloc(sizeof(scalar_sphere) * Scene.SphereCount);
+    if (!Copy) return false;
+    memcpy(Copy, Scene.ScalarSpheres, sizeof(scalar_sphere) * Scene.SphereCount);
+    if (g_SceneBuilt[SceneIndex]) free(g_Scenes[SceneIndex].ScalarSpheres);
+    g_Scenes[SceneIndex] = Scene;
+    g_Scenes[SceneIndex].ScalarSpheres = Copy;
+    g_SceneBuilt[SceneIndex] = true;
+    g_SceneGenerations[SceneIndex] += 1;
+    return true;
+}
+
+// Drop a replaced slot: the next GetScene(SceneIndex) rebuilds the built-in / synthetic scene.
+void ResetScene(u32 SceneIndex) {
+    if (SceneIndex >= SceneCount || !g_SceneBuilt[SceneIndex]) return;
+    free(g_Scenes[SceneIndex].ScalarSpheres);
+    g_Scenes[SceneIndex].ScalarSpheres = nullptr;
+    g_SceneBuilt[SceneIndex] = false;
+    g_SceneGenerations[SceneIndex] += 1;
+}
+
+// FNV-1a over the sphere table and the sky flag: ties a checkpoint to the scene it was rendered from.
+u64 HashScene(const scene &Scene) {
+    u64 H = 0xCBF29CE484222325ULL;
+    const u8 *P = (const u8 *)Scene.ScalarSpheres;
+    for (size_t i = 0; i < sizeof(scalar_sphere) * (size_t)Scene.SphereCount; ++i) { H ^= P[i]; H *= 0x100000001B3ULL; }
+    H ^= Scene.UseSkyColor ? 1u : 0u; H *= 0x100000001B3ULL;
+    return H ? H : 1;
+}
+
+// main.cpp:776-780 (orbit position) and 811-822 (basis + film).
+void ComputeCamera(const scene &Scene, f32 Distance, f32 XAngle, f32 YHeight, u32 Width, u32 Height, srt_camera *Out) {
+    memset(Out, 0, sizeof(*Out));
+    const vec LookAt = { Scene.LookAt.x, Scene.LookAt.y, Scene.LookAt.z };
+    const f32 Px = cosf(XAngle) * Distance, Pz = sinf(XAngle) * Distance;
+    const vec Position = { Px + LookAt.x, YHeight + LookAt.y, Pz + LookAt.z };
+    const vec Z = Normalize(Sub(Position, LookAt));
+    const vec X = Normalize(Cross({ 0.0f, 1.0f, 0.0f }, Z));
+    const vec Y = Normalize(Cross(Z, X));
+    const vec FilmCenter = Sub(Position, Z);
+    f32 FilmW = 1.0f, FilmH = 1.0f;
+    if (Width > Height) FilmH = (f32)Height / (f32)Width;
+    else FilmW = (f32)Width / (f32)Height;
+    const vec *Src[5] = { &Position, &Z, &X, &Y, &FilmCenter };
+    f32 *Dst[5] = { Out->camera_position, Out->camera_z, Out->camera_x, Out->camera_y, Out->film_center };
+    for (int i = 0; i < 5; ++i) { Dst[i][0] = Src[i]->x; Dst[i][1] = Src[i]->y; Dst[i][2] = Src[i]->z; }
+    Out->film_w = FilmW;
+    Out->film_h = FilmH;
+}
+
 void BuildScene(u32 SceneIndex, scene *Out) {
     memset(Out, 0, sizeof(*Out));
     switch (SceneIndex) {

@@ -180,3 +180,22 @@ def test_bundle_fuzz_against_non_bundle(srt, monkeypatch):
         on = _run(srt, env, monkeypatch, spheres, sky, 8, 1, cam, w, h, launches)
         off = _run(srt, {"SRT_BUNDLE": "0"}, monkeypatch, spheres, sky, 8, 1, cam, w, h, launches)
         assert _same(off, on) == {}, (case, w, h, launches, env)
+
+
+def test_bundle_lanes_past_the_table_end(srt, oracle, monkeypatch):
+    """n_pad % 128 != 0 (scene 2: 482 spheres -> 488): in the last 128-sphere round of the level-0 scan the lanes past
+    the table end used to test a dummy {0, 0, r' = -1} record, and |nou| <= wl * eps - 1 HOLDS for a far camera that
+    looks at the origin through a coarse image (eps ~ 0.05) -- queueing sphere indices >= n_pad.  Such lanes now
+    contribute nothing and padding radii are -1e30.  Far cameras, tiny images, every slab axis: bundle mode equals the
+    CPU oracle and the non-bundle kernel."""
+    spheres, sky, hdr = srt.host_scene(2)
+    assert len(spheres) % 128 != 0 and ((len(spheres) + 7) // 8 * 8) % 128 != 0
+    for axis in ("0", "1", "2"):
+        for (pos, w, h) in (((60.0, 25.0, 40.0), 16, 16), ((0.0, 100.0, 3.0), 24, 12), ((-35.0, 2.0, -80.0), 64, 36), ((20.0, 20.0, 20.0), 8, 8)):
+            cam = _look_camera(srt, pos, (0.0, 0.0, 0.0), w, h, film_w=1.0)
+            on = _run(srt, {"SRT_BUNDLE": "6", "SRT_SLAB_AXIS": axis}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, 64)])
+            off = _run(srt, {"SRT_BUNDLE": "0", "SRT_SLAB_AXIS": axis}, monkeypatch, spheres, sky, 8, 1, cam, w, h, [(0, 64)])
+            assert _same(off, on) == {}, (axis, pos, w, h)
+        o = oracle.render(spheres, sky, 8, 1, cam, w, h, 0, 64)
+        assert _same(o, on) == {}, axis
+    monkeypatch.delenv("SRT_SLAB_AXIS", raising=False)

@@ -99,12 +99,34 @@ def test_checkpoint_round_trip_and_rejects_damage(srt, tmp_path):
     assert a2.tobytes() == acc.tobytes()
     assert h == {"width": 13, "height": 7, "samples": 11, "scene_index": 2, "lane_width": 4, "fma_dot": 0, "stream_base": (1 << 40) + 3}
     raw = path.read_bytes()
-    assert raw[:8] == b"SRTCKPT1" and len(raw) == 8 + 32 + acc.nbytes
-    for damaged in (raw[:-4], raw + b"\0", b"XRTCKPT1" + raw[8:], raw[:20]):
+    # "SRTCKPT2" | 4 x u32 | u64 stream base | 2 x u32 | u64 scene hash | payload
+    assert raw[:8] == b"SRTCKPT2" and len(raw) == 8 + 40 + acc.nbytes
+    assert int.from_bytes(raw[40:48], "little") == srt.host_scene_hash(2) != 0
+    huge = bytearray(raw)
+    huge[8:16] = (40000).to_bytes(4, "little") + (40000).to_bytes(4, "little")    # header asks for 25.6 GB: rejected by file size, before any allocation
+    for damaged in (raw[:-4], raw + b"\0", b"XRTCKPT2" + raw[8:], b"SRTCKPT1" + raw[8:], raw[:20], bytes(huge)):
         bad = tmp_path / "bad.ckpt"
         bad.write_bytes(damaged)
         with pytest.raises(srt.SrtError):
             srt.load_checkpoint(bad)
+
+
+def test_scene_hash_follows_the_sphere_table(srt, tmp_path):
+    """The checkpoint's scene hash (FNV-1a of the sphere records + sky flag) changes when the slot's scene does."""
+    h3 = srt.host_scene_hash(3)
+    assert h3 == srt.host_scene_hash(3) and h3 != srt.host_scene_hash(2)
+    path = tmp_path / "s.scene"
+    srt.save_scene_file(3, path)
+    text = path.read_text().splitlines()
+    text[-1] = text[-1].replace("sphere ", "sphere  ", 1)       # same values: same hash
+    path.write_text("\n".join(text) + "\n")
+    srt.load_scene_file(3, path)
+    assert srt.host_scene_hash(3) == h3
+    path.write_text("\n".join(text[:-1]) + "\n")               # one sphere fewer
+    srt.load_scene_file(3, path)
+    assert srt.host_scene_hash(3) != h3
+    srt.reset_scene(3)
+    assert srt.host_scene_hash(3) == h3
 
 
 def test_magic_division_is_exact():

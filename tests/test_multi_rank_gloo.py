@@ -1,6 +1,7 @@
-"""CPU, world_size 2 over gloo: the N>1 host path (sample sharding plan + sum-reduce +
-resolve).  The CPU oracle stands in for the device renderer; the collective, the plan and the
-tolerance are the ones bench.py uses on the GPUs."""
+"""CPU, world_size 2 over gloo: the N>1 host logic -- both partitions of a frame (row bands: sum-reduce of disjoint
+rows == gather, bit-identical; samples: sum-reduce + resolve, within tolerance).  The CPU oracle stands in for the
+device renderer; on the GPUs the same plan runs inside the library (srt_set_partition / srt_gather_rgba /
+srt_reduce_accum over NCCL, tests/test_gpu_multi.py)."""
 import os
 import sys
 
@@ -31,9 +32,21 @@ def _worker(rank, world, port, out_dir):
     srt.sharding.reduce_sum(dist, t, dst=0)
     r = torch.tensor([rays], dtype=torch.int64)
     dist.reduce(r, dst=0)
+    # image partition: this rank's row bands of the exact image, zero elsewhere; integer sum of the RGBA8 words
+    exact = O.render(sp, sky, 8, 1, cam, W, H, 0, SPP, threads=1)
+    rows = srt.sharding.band_rows(rank, world, H)
+    mine_rgba = np.zeros((H, W), np.int64)
+    mine_rgba[rows] = exact["rgba"][rows]
+    mine_acc = np.zeros((H, W, 4), np.float32)
+    mine_acc[rows] = exact["accum"][rows]
+    tr, ta = torch.from_numpy(mine_rgba), torch.from_numpy(mine_acc)
+    srt.sharding.reduce_sum(dist, tr, dst=0)
+    srt.sharding.reduce_sum(dist, ta, dst=0)
     if rank == 0:
         np.save(os.path.join(out_dir, "sum.npy"), t.numpy())
         np.save(os.path.join(out_dir, "rays.npy"), r.numpy())
+        np.save(os.path.join(out_dir, "band_rgba.npy"), tr.numpy())
+        np.save(os.path.join(out_dir, "band_acc.npy"), ta.numpy())
     dist.barrier()
     dist.destroy_process_group()
 
@@ -61,6 +74,21 @@ def test_two_rank_sample_sharding(tmp_path, oracle):
     mse = float(np.mean((total[..., :3].astype(np.float64) - exact["accum"][..., :3].astype(np.float64)) ** 2))
     peak = float(max(exact["accum"][..., :3].max(), 1.0))
     assert 10 * np.log10(peak * peak / max(mse, 1e-30)) >= 50.0
+    # row bands: the reduced buffers ARE the exact image
+    assert np.array_equal(np.load(tmp_path / "band_rgba.npy").astype(np.uint32), exact["rgba"])
+    assert np.array_equal(np.load(tmp_path / "band_acc.npy").view(np.uint32), exact["accum"].view(np.uint32))
+
+
+def test_band_plan_covers_every_row_once():
+    import importlib
+    srt = importlib.import_module("simd-ray-tracer_b200")
+    for world in (1, 2, 3, 4, 8):
+        for height in (1, 4, 5, 135, 720, 2160):
+            seen = sorted(y for r in range(world) for y in srt.sharding.band_rows(r, world, height))
+            assert seen == list(range(height))
+    # 4K over 8 ranks: 540 block rows -> 67 or 68 each (0.7 % imbalance at most)
+    sizes = [len(srt.sharding.band_rows(r, 8, 2160)) for r in range(8)]
+    assert max(sizes) - min(sizes) <= 4 and sum(sizes) == 2160
 
 
 def test_plan_covers_every_sample_once():
