@@ -1,21 +1,30 @@
 #!/usr/bin/env python3
 """bench.py -- headline benchmark of the B200 path-tracing backend.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME] [--partition bands|samples]
     python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
 
 Metric (BASELINE.json): Mrays/s -- path segments per second, a "ray" counted exactly like the
 reference's RaysCastInThread (main.cpp:390).  Default workload = BASELINE.json configs[2], the
 configuration the multi-GPU / %-of-FP32-peak metric is quoted on: synthetic 1,024-sphere
-scene, 3840x2160, 256 spp, samples sharded over the N GPUs (strong scaling: the job is
-fixed, rank g renders samples k = g mod N into an f32 SUM buffer, one NCCL reduce to rank 0,
-which resolves mean + tonemap).  At N = 1 the exact running mean of main.cpp:484-489 is used.
-One "step" = one complete render of the workload.  Prints ONE JSON line on rank 0.
+scene, 3840x2160, 256 spp.  One "step" = one complete render of the workload (strong scaling: the
+job is fixed).  Over N GPUs the frame is partitioned INSIDE the library (include/srt_backend.h):
 
-Other workloads (--workload): demo1080 (configs[1]), stress64k (configs[4]), and the
-progressive-latency protocol of configs[3] is always measured as `frame_latency_1080p`.
+  --partition bands    (default) rank g renders all samples of every N-th row of 8x4-pixel blocks with the exact
+                       running mean, srt_gather_rgba(0) = ONE NCCL sum-reduce of the RGBA8 words (33 MB at 4K)
+                       issued by libsrt_cuda.so on the render stream: the image is bit-identical to N = 1;
+  --partition samples  rank g renders samples k = g (mod N) into an f32 SUM, srt_reduce_accum(0) (132.7 MB),
+                       srt_resolve_sum on rank 0: within the stated tolerance (<= 2 LSB, PSNR >= 50 dB).
+
+torch.distributed (NCCL) is used for the rendezvous only: barriers, the max-over-ranks of the timers and the
+broadcast of the library's NCCL unique id -- never for pixels.  Prints ONE JSON line on rank 0.
+
+Other workloads (--workload): demo720_1spp (configs[0]), demo1080_64spp (configs[1]), stress64k_1080_16spp
+(configs[4]); they are also measured (one short run each, with the CPU reference's rate on the same scene) in the
+default line's `workloads` block, and the progressive protocol of configs[3] as `frame_latency_1080p`.
 """
 import argparse
+import hashlib
 import importlib
 import json
 import os
@@ -31,13 +40,18 @@ sys.path.insert(0, ROOT)
 
 WORKLOADS = {
     # name: (scene index in the host mirror, width, height, spp, description)
-    "synth1k_4k_256spp": (3, 3840, 2160, 256, "BASELINE configs[2]: synthetic 1,024-sphere scene, 3840x2160, 256 spp, sample-sharded"),
+    "synth1k_4k_256spp": (3, 3840, 2160, 256, "BASELINE configs[2]: synthetic 1,024-sphere scene, 3840x2160, 256 spp"),
+    "demo720_1spp": (0, 1280, 720, 1, "BASELINE configs[0]: built-in demo scene 0 (RGB glass, 5 spheres), 1280x720, 1 spp -- the reference's start-up state"),
     "demo1080_64spp": (0, 1920, 1080, 64, "BASELINE configs[1]: built-in demo scene 0 (RGB glass, 5 spheres), 1920x1080, 64 spp"),
     "stress64k_1080_16spp": (4, 1920, 1080, 16, "BASELINE configs[4]: 65,536-sphere brute-force scene, 1920x1080, 16 spp"),
-    "smoke": (3, 480, 270, 8, "tiny smoke workload (not a benchmark)"),
+    "smoke": (3, 480, 270, 16, "tiny smoke workload (not a benchmark)"),
 }
-FLOP_PER_TEST = 20          # always-executed FP32 flops of one ray-sphere test
+# golden records of tests/golden/ref_full_hashes.json (SHA-256 of the buffers the reference's own code renders)
+PARITY_KEYS = {"synth1k_4k_256spp": "bench_synth1k_4k_256spp", "demo720_1spp": "s0_w8f_1280x720_1spp",
+               "demo1080_64spp": "s0_w8f_1920x1080_64spp", "smoke": "s3_w8f_480x270_16spp"}
+FLOP_PER_TEST = 20          # always-executed FP32 flops of one reference ray-sphere test
 LANE_WIDTH, FMA_DOT = 8, True   # the x64 AVX2 profile (SIMD_WIDTH 8, FMA dot)
+ROOFLINE_PROFILE = os.path.join(ROOT, "profiles", "r2_roofline_bench.json")   # scripts/merge_roofline.py
 
 
 def dist_env():
@@ -94,47 +108,68 @@ def load_measured_peaks():
         return {}
 
 
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def load_goldens():
+    try:
+        with open(os.path.join(ROOT, "tests", "golden", "ref_full_hashes.json")) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {}
+
+
 # ---------------------------------------------------------------------------------------------
 # reference arm / CPU baseline: the reference's OWN compiled CPU code (oracle/_ref), all host
 # threads, on a bounded sample of the same workload.  (bench.py may execute oracle/ only here.)
 # ---------------------------------------------------------------------------------------------
-def cpu_reference_run(srt, scene_idx, width, height, budget_s, repeats=1):
+REF_VARIANTS = [("w8", 1, "RenderTile SIMD_WIDTH=8, g++ -O3 -mavx2 -mfma"), ("w8", 0, "RenderTileScalar, g++ -O3 -mavx2 -mfma"),
+                ("w4", 1, "RenderTile SIMD_WIDTH=4, g++ -O3 -msse4.2"), ("w4", 0, "RenderTileScalar, g++ -O3 -msse4.2")]
+
+
+def cpu_reference_run(srt, scene_idx, width, height, budget_s, repeats=1, probe_s=0.6):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import orclib
     if not orclib.have_ref():
         raise RuntimeError("oracle/_ref is missing (build it where /root/reference exists: python oracle/build_ref.py)")
     sp, sky, hdr = srt.host_scene(scene_idx)
     cores = os.cpu_count() or 1
-    best = None
-    # The reference ships two lane widths and two tile callbacks; time them all on a small
-    # probe and keep the fastest as "the reference CPU path" (BASELINE.md section 4).
-    probe_w, probe_h = 160, 90
-    for tag in ("w8", "w4"):
-        R = orclib.Ref(tag, cores)
-        R.set_scene(1, sp, sky, hdr)
-        for simd in (1, 0):
-            r = R.render(1, probe_w, probe_h, 1, simd=simd, threads=cores, flags=0)
-            rate = r["rays"] / max(r["ms"], 1e-6)      # rays per ms
-            if best is None or rate > best[0]:
-                best = (rate, tag, simd, R)
-    rate, tag, simd, R = best
-    # Size the sample: same scene and camera, the workload's aspect ratio at reduced
-    # resolution / spp so that one run costs about budget_s of wall time.
-    # Enough 32x32 tiles (main.cpp:9) to keep every worker thread busy.
+    # Sample geometry: same scene and camera, the workload's aspect ratio at reduced resolution with enough 32x32 tiles
+    # (main.cpp:9) to keep every worker thread busy.
     div = 4
     while div > 1 and ((width // div + 31) // 32) * ((height // div + 31) // 32) < 4 * cores:
         div //= 2
     w, h = max(32, width // div), max(32, height // div)
-    rays_per_spp = 2.2 * w * h
-    spp = int(max(1, min(64, budget_s * 1000.0 * rate / rays_per_spp)))
+    # The reference ships two lane widths and two tile callbacks.  Each of the four is timed on the sample geometry for
+    # >= probe_s seconds (a few-millisecond probe let the choice flip between runs); the fastest is "the reference CPU path".
+    refs, rates = {}, {}
+    for tag, simd, name in REF_VARIANTS:
+        if tag not in refs:
+            refs[tag] = orclib.Ref(tag, cores)
+            refs[tag].set_scene(1, sp, sky, hdr)
+        R = refs[tag]
+        rays = ms = 0.0
+        spp = 1
+        while ms < probe_s * 1e3:
+            r = R.render(1, w, h, spp, simd=simd, threads=cores, flags=0)
+            rays += r["rays"]; ms += r["ms"]
+            spp = min(64, spp * 2)
+        rates[name] = rays / ms / 1e3      # Mrays/s
+    best = max(rates, key=rates.get)
+    tag, simd, _ = next(v for v in REF_VARIANTS if v[2] == best)
+    R = refs[tag]
+    # samples per pixel of the timed sample: about budget_s of wall time at the probed rate
+    one = R.render(1, w, h, 1, simd=simd, threads=cores, flags=0)
+    spp = int(max(1, min(256, budget_s * rates[best] * 1e6 / max(one["rays"], 1))))
     results = []
     for _ in range(repeats):
         r = R.render(1, w, h, spp, simd=simd, threads=cores, flags=0)
         results.append((r["rays"], r["ms"]))
     rays = sum(x[0] for x in results)
     ms = sum(x[1] for x in results)
-    kind = f"reference ({'RenderTile SIMD_WIDTH=' + tag[1:] if simd else 'RenderTileScalar'}, g++ -O3 {'-mavx2 -mfma' if tag == 'w8' else '-msse4.2'}, as-shipped RNG)"
-    return dict(mrays=rays / ms / 1e3, rays=rays, ms=ms, cores=cores, sample=f"{w}x{h}, {spp} spp, same scene/camera, {len(results)} run(s)", variant=kind,
+    return dict(mrays=rays / ms / 1e3, rays=rays, ms=ms, cores=cores, sample=f"{w}x{h}, {spp} spp, same scene/camera, {len(results)} run(s)",
+                variant=f"reference ({best}, as-shipped RNG)", variant_rates_mrays={k: round(v, 3) for k, v in rates.items()},
                 per_run=[dict(rays=a, ms=b) for a, b in results])
 
 
@@ -145,7 +180,7 @@ def run_reference_arm(args):
     srt = importlib.import_module("simd-ray-tracer_b200")
     scene_idx, w, h, spp, desc = WORKLOADS[args.workload]
     for _ in range(args.warmup):
-        cpu_reference_run(srt, scene_idx, w, h, budget_s=1.0)
+        cpu_reference_run(srt, scene_idx, w, h, budget_s=0.5, probe_s=0.2)
     t0 = time.perf_counter()
     r = cpu_reference_run(srt, scene_idx, w, h, budget_s=max(2.0, 40.0 / max(1, args.steps)), repeats=args.steps)
     wall = time.perf_counter() - t0
@@ -156,7 +191,8 @@ def run_reference_arm(args):
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "spheres": int(len(sp)), "width": w, "height": h, "spp": spp,
                    "step": "bounded sample of the workload on the host CPU: " + r["sample"]},
-        "cpu_baseline": {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"], "variant": r["variant"]},
+        "cpu_baseline": {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"], "variant": r["variant"],
+                         "variant_rates_mrays": r["variant_rates_mrays"]},
         "e2e": {"value": r["mrays"], "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "wall_s": wall,
     }
@@ -167,6 +203,70 @@ def run_reference_arm(args):
 # ---------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------
+def expected_kernel(n_pad, spp_per_launch):
+    """Name of the kernel srt_render picks for the AVX2 profile (csrc/srt_backend.cu: srt_render, plan_bundle)."""
+    if n_pad < 64:
+        return "render_paths<8, 1, 0, 4, 4>" if n_pad <= 16 else "render_paths<8, 1, 1, 4, 3>"
+    bundle = 1 if (n_pad >= 384 and spp_per_launch >= 8 and os.environ.get("SRT_BUNDLE", "1") != "0") else 0
+    if n_pad > 8192:
+        return f"render_pool<8, 1, 256, 2, 1, {bundle}>"
+    return f"render_pool<8, 1, 896, 1, 0, {bundle}>"
+
+
+def roofline_block(info, n_pad, rays_per_launch, kms, kernel_name, peaks):
+    """FP32 roofline of the dominant kernel.  `frac` is MEASURED: the FMA-pipe utilisation ncu reports for this very
+    launch (profiles/r2_roofline_bench.json, produced by scripts/merge_roofline.py from the committed ncu CSV); it is
+    merged only if the profile's kernel name matches and its duration is within 5 % of the live kernel time."""
+    sm_max_mhz = float(peaks.get("sm_max_mhz", 1965.0))
+    peak_tflops = info["sm_count"] * 128 * 2 * sm_max_mhz * 1e6 / 1e12
+    tests = rays_per_launch * n_pad
+    algorithmic = FLOP_PER_TEST * tests / (kms * 1e-3) / 1e12
+    block = {
+        "bound": "fp32", "kernel": kernel_name, "unit": "TFLOP/s", "peak": peak_tflops,
+        "peak_source": f"{info['sm_count']} SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); no tensor-core or "
+                       "HBM roof applies: the loop has no dense contraction and its scene is shared-memory resident",
+        "achieved": None, "frac": None, "traffic": None,
+        "kernel_ms": kms, "tests_per_launch": tests,
+        "achieved_algorithmic": algorithmic, "algorithmic_flop_per_test": FLOP_PER_TEST,
+        "algorithmic_note": "SURVEY 8(d): 20 always-executed flops per reference ray-sphere test x tests per launch / live kernel time.  NOT a "
+                            "utilisation: every sphere is tested against every ray, but with a conservative 2-FMA slab test (once per pixel "
+                            "for the samples of a primary pass); ~2 % of the pairs reach a 7-FMA filter and ~0.2 % the reference's sequence "
+                            "(bit-exact results: DESIGN.md 5.3, srt_filter_audit)",
+        "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
+    }
+    prof = None
+    try:
+        with open(ROOFLINE_PROFILE) as f:
+            prof = json.load(f)
+    except (OSError, ValueError):
+        block["profile"] = "missing: " + os.path.relpath(ROOFLINE_PROFILE, ROOT)
+    if prof is not None:
+        same_kernel = prof.get("kernel", "").replace(" ", "") == kernel_name.replace(" ", "")
+        drift = abs(prof.get("duration_ms", 0.0) - kms) / kms if kms > 0 else 1.0
+        if same_kernel and drift <= 0.05:
+            frac = prof["fma_pipe_pct"] / 100.0
+            executed = prof["executed_flop"] / (prof["duration_ms"] * 1e-3) / 1e12
+            block.update({
+                "frac": frac, "achieved": frac * peak_tflops,
+                "frac_definition": "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_elapsed of this launch under ncu; `achieved` = frac x peak "
+                                   "(FP32-pipe issue bandwidth in use, in TFLOP/s-equivalents)",
+                "fma_pipe_pct": prof["fma_pipe_pct"], "issue_active_pct": prof.get("issue_active_pct"),
+                "inst_executed_pipe_fma_pct": prof.get("inst_fma_pct"), "alu_pipe_pct": prof.get("alu_pipe_pct"),
+                "achieved_executed_tflops": executed, "frac_executed_flops": executed / peak_tflops,
+                "executed_flop_per_test": prof["executed_flop"] / tests if tests else None,
+                "executed_flop_source": "smsp__sass_thread_inst_executed_op_{ffma,fmul,fadd,ffma2,fmul2,fadd2}_pred_on.sum "
+                                        "(2 ffma + fmul + fadd + 4 ffma2 + 2 fmul2 + 2 fadd2)",
+                "work_avoidance_factor": algorithmic / executed if executed else None,
+                "traffic": prof.get("dram_bytes"), "l2_bytes": prof.get("lts_bytes"), "algorithmic_bytes": prof.get("algorithmic_bytes"),
+                "profile": {"file": os.path.relpath(ROOFLINE_PROFILE, ROOT), "source": prof.get("source"), "duration_ms_under_ncu": prof.get("duration_ms"),
+                            "duration_drift": drift},
+            })
+        else:
+            block["profile"] = (f"NOT merged: {os.path.relpath(ROOFLINE_PROFILE, ROOT)} describes kernel '{prof.get('kernel')}' at {prof.get('duration_ms')} ms, "
+                                f"this run launched '{kernel_name}' at {kms:.2f} ms (name match {same_kernel}, drift {drift:.3f} > 0.05): re-profile")
+    return block
+
+
 def run_gpu_arm(args):
     import torch
     rank, local_rank, world = dist_env()
@@ -183,7 +283,8 @@ def run_gpu_arm(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     scene_idx, W, H, SPP, desc = WORKLOADS[args.workload]
-    shard = srt.sharding.plan(rank, n_gpus, SPP)
+    bands = args.partition == "bands" or n_gpus == 1
+    shard = srt.sharding.plan(rank, n_gpus, SPP) if not bands else None
     spheres, sky, hdr = srt.host_scene(scene_idx)
     camera = srt.host_camera(scene_idx, W, H)
     n_pad = (len(spheres) + 7) // 8 * 8
@@ -192,12 +293,16 @@ def run_gpu_arm(args):
     info0 = b.device_info()
     b.set_scene(spheres, sky, LANE_WIDTH, FMA_DOT)
     b.resize(W, H)
-    # torch owns the framebuffers so that NCCL can reduce them in place
-    accum = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
-    rgba = torch.zeros((H, W), dtype=torch.int32, device="cuda")
-    torch.cuda.synchronize()
-    b.bind_device_buffers(accum.data_ptr(), rgba.data_ptr())
-    ext_stream = torch.cuda.ExternalStream(b.stream_ptr)      # NCCL ops ordered on the backend's stream
+    if n_gpus > 1:
+        # the library's own communicator: rank 0 makes the NCCL id, torch.distributed only carries it to the other ranks
+        uid = torch.zeros(srt.COMM_ID_BYTES, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            uid.copy_(torch.frombuffer(bytearray(srt.comm_unique_id()), dtype=torch.uint8))
+        dist.broadcast(uid, src=0)
+        b.comm_init_rank(n_gpus, rank, uid.cpu().numpy().tobytes())
+        if bands:
+            b.set_partition(rank, n_gpus)
+    ext_stream = torch.cuda.ExternalStream(b.stream_ptr)      # the backend's stream: renders and the library's collectives
 
     def barrier():
         torch.cuda.synchronize()
@@ -209,18 +314,17 @@ def run_gpu_arm(args):
 
     def step():
         """One complete render of the workload, inputs resident in HBM."""
-        with torch.cuda.stream(ext_stream):
-            accum.zero_()
-        if n_gpus == 1:
-            b.render(camera, 0, SPP, stride=1, mode=srt.ACCUM_MEAN)
-            ms, rays = b.wait()
+        if bands:
+            b.render(camera, 0, SPP, stride=1, mode=srt.ACCUM_MEAN)      # overwrites this rank's rows; foreign rows stay zero
+            if n_gpus > 1:
+                b.gather_rgba(0)
         else:
+            b.reset()                                                     # the SUM accumulates: clear it
             b.render(camera, shard["first"], shard["count"], stride=shard["stride"], mode=srt.ACCUM_SUM)
-            with torch.cuda.stream(ext_stream):
-                srt.sharding.reduce_sum(dist, accum, dst=0)
+            b.reduce_accum(0)
             if rank == 0:
                 b.resolve_sum(SPP)
-            ms, rays = b.wait()
+        ms, rays = b.wait()
         kernel_ms.append(ms)
         kernel_rays.append(rays)
         return rays
@@ -233,8 +337,8 @@ def run_gpu_arm(args):
     if rank == 0:
         sampler.start()
     kernel_ms.clear(); kernel_rays.clear()
-    # Device-side clock: CUDA events on the stream every launch of a step goes to (the backend's
-    # own stream, which also carries the memset and the NCCL reduce); wall clock kept beside it.
+    # Device-side clock: CUDA events on the stream every launch of a step goes to (the backend's own stream, which also
+    # carries the library's NCCL reduce); wall clock kept beside it.
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record(ext_stream)
@@ -248,6 +352,25 @@ def run_gpu_arm(args):
     clocks = sampler.stop() if rank == 0 else None
     launches = b.device_info()["launches"] - launches0
 
+    # ---- parity of the image the timed steps produced (rank 0 holds it) ---------------------------
+    parity = None
+    if rank == 0:
+        gold = load_goldens().get(PARITY_KEYS.get(args.workload, ""), None)
+        rgba_hash = sha(b.read_rgba8())
+        parity = {"rgba_sha256": rgba_hash}
+        if gold is None:
+            parity.update({"checked": False, "why": "no golden record for this workload in tests/golden/ref_full_hashes.json"})
+        elif bands:
+            acc_ok = None
+            if n_gpus == 1:
+                acc_ok = sha(b.read_accum()) == gold["accum"]
+            parity.update({"checked": True, "against": "tests/golden/ref_full_hashes.json:" + PARITY_KEYS[args.workload]
+                           + " (SHA-256 of the buffers the reference's own compiled code renders for this job)",
+                           "rgba_equal": rgba_hash == gold["rgba"], "accum_equal": acc_ok, "tolerance": "bit-exact"})
+        else:
+            parity.update({"checked": False, "why": "sample partition: sum-then-divide differs from the running mean within the stated tolerance "
+                                                    "(<= 2 LSB, PSNR >= 50 dB: tests/test_gpu_multi.py)"})
+
     t = torch.tensor([elapsed, float(rays_local), float(launches), float(np.mean(kernel_ms)), wall_elapsed], dtype=torch.float64, device="cuda")
     if dist is not None:
         tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -257,6 +380,10 @@ def run_gpu_arm(args):
         elapsed, rays_total, launches_total, kms = t[0].item(), t[1].item(), t[2].item(), t[3].item()
     value = rays_total / elapsed / 1e6
     ms_per_step = elapsed * 1e3 / args.steps
+    if parity is not None and parity.get("checked"):
+        gold = load_goldens()[PARITY_KEYS[args.workload]]
+        parity["rays_equal"] = int(round(rays_total / args.steps)) == gold["rays"]
+        parity["pass"] = bool(parity["rgba_equal"] and parity["rays_equal"] and parity["accum_equal"] in (True, None))
 
     # ---- end to end through the C ABI with HOST buffers (rank-local pinned memory) ------------
     pin_scene = torch.empty(spheres.nbytes, dtype=torch.uint8).pin_memory()
@@ -270,14 +397,14 @@ def run_gpu_arm(args):
 
     def e2e_step():
         b.set_scene(scene_host, sky, LANE_WIDTH, FMA_DOT)         # H2D: scene table
-        with torch.cuda.stream(ext_stream):
-            accum.zero_()
-        if n_gpus == 1:
+        if bands:
             b.render(cam_host, 0, SPP, stride=1, mode=srt.ACCUM_MEAN)   # H2D: camera (kernel params)
+            if n_gpus > 1:
+                b.gather_rgba(0)
         else:
+            b.reset()
             b.render(cam_host, shard["first"], shard["count"], stride=shard["stride"], mode=srt.ACCUM_SUM)
-            with torch.cuda.stream(ext_stream):
-                srt.sharding.reduce_sum(dist, accum, dst=0)
+            b.reduce_accum(0)
             if rank == 0:
                 b.resolve_sum(SPP)
         _, rays = b.wait()
@@ -300,76 +427,28 @@ def run_gpu_arm(args):
         tsum = t.clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
         e2e_elapsed, e2e_rays = tmax[0].item(), tsum[1].item()
     e2e_value = e2e_rays / e2e_elapsed / 1e6
-    checksum = int(img_host.view(np.uint8)[::997].astype(np.uint64).sum()) if rank == 0 else 0
+    e2e_rgba_equal = (sha(img_host) == parity["rgba_sha256"]) if rank == 0 else None
 
+    comm_info = b.comm_info() if n_gpus > 1 else None
+    if n_gpus > 1:
+        b.comm_destroy()
     if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
+        b.close()
+        dist.destroy_process_group()
         return 0
+    if n_gpus > 1:
+        b.set_partition(0, 1)
 
-    # ---- roofline of the dominant kernel (render_paths): FP32 CUDA-core pipe ------------------
     peaks = load_measured_peaks()
-    sm_max_mhz = float(peaks.get("sm_max_mhz", 1965.0))
-    peak_tflops = info0["sm_count"] * 128 * 2 * sm_max_mhz * 1e6 / 1e12
     rays_per_launch = float(np.mean(kernel_rays))
-    achieved = FLOP_PER_TEST * rays_per_launch * n_pad / (kms * 1e-3) / 1e12
-    pair_kernel = n_pad >= 64
-    primary_per_launch = float(W * H * SPP) / max(1, n_gpus)   # one render launch per step per rank
-    issue_cycles_per_sphere_pass = (info0["sm_count"] * 4 * sm_max_mhz * 1e6 * 64) / (rays_per_launch * n_pad / (kms * 1e-3))
-    # bundle mode (csrc/srt_bundle.cuh; auto from 384 spheres and 8 samples per launch): the primary passes run the
-    # level-1 test once per (pixel, sphere) for all samples of the pixel, 1/32 of the spheres per lane
-    bundle = pair_kernel and n_pad >= 384 and SPP // max(1, n_gpus) >= 8 and os.environ.get("SRT_BUNDLE", "1") != "0"
-    f_prim = min(1.0, primary_per_launch / max(1.0, rays_per_launch))
-    floor_pass = (8.06 * (1.0 - f_prim) + 0.35 * f_prim) if bundle else (8.06 if pair_kernel else 30.0)
-    exec_flop = (4.0 * (1.0 - f_prim) + 6.0 / 64.0 * f_prim) if bundle else (4.0 if pair_kernel else 20.0)
-    roofline = {
-        "bound": "fp32",
-        "kernel": ("render_pool<8,true> (CTA-owned path slots, warp passes of 64 rays, two rays per thread: level-1 slab test of every "
-                   "sphere (2 FFMA2 + 2 FSETP per sphere per ray pair"
-                   + ("; bundle mode: a primary pass holds the samples of one pixel and runs the test once per (pixel, sphere), "
-                      "1/32 of the spheres per lane" if bundle else "")
-                   + "), level-2 fused 7-FMA filter on the survivors, the reference's arithmetic on what is left"
-                   + ("; tables streamed through per-warp TMA stages)" if n_pad > 8192 else "; tables resident in shared memory)")
-                   if pair_kernel else "render_paths<8,true,true> (packed FFMA2 intersection loop)"),
-        "achieved": achieved, "peak": peak_tflops, "unit": "TFLOP/s", "frac": achieved / peak_tflops,
-        "peak_source": f"{info0['sm_count']} SMs x 128 FP32 lanes x 2 x {sm_max_mhz:.0f} MHz (sm_max_mhz of MEASURED_PEAKS.json); "
-                       "no tensor-core or HBM roof applies: the loop has no dense contraction and its scene is shared-memory resident",
-        "algorithmic_flop_per_test": FLOP_PER_TEST, "tests_per_launch": rays_per_launch * n_pad,
-        "executed_flop_per_test": exec_flop,
-        "frac_executed": exec_flop * rays_per_launch * n_pad / (kms * 1e-3) / 1e12 / peak_tflops,
-        "bundle_mode": bool(bundle), "primary_ray_fraction": f_prim,
-        "issue_cycles_per_sphere_per_warp_pass": issue_cycles_per_sphere_pass,
-        "issue_floor_cycles_per_sphere_per_warp_pass": floor_pass,
-        "issue_slot_frac": floor_pass / issue_cycles_per_sphere_pass,
-        "issue_bound_note": ("`achieved`/`frac` count the reference's 20 flop per ray-sphere test (SURVEY 8d) and exceed the FP32 peak "
-                             "because the kernel does not execute them: every sphere is tested against every ray with a conservative "
-                             "2-FMA slab test (4 executed flop), ~2 % go on to a 7-FMA filter, ~0.2 % to the reference's 20-flop "
-                             "sequence (bit-exact results; soundness proof DESIGN.md 5.3, on-device audit srt_filter_audit).  The "
-                             "binding resource is the SM sub-partition's issue port: a packed FFMA2 holds it for 2 cycles and LDS / "
-                             "FSETP / LOP3 are not issued in its shadow (scripts/microbench/issue_mix.cu), so the level-1 floor is "
-                             "2x2 + 2 + 1 + 0.75 + loop = 8.06 issue cycles per sphere per 64 rays; `issue_slot_frac` = that floor / "
-                             "the measured whole-kernel cycles per sphere per 64 rays (regenerate, level 2, select, shade included)"
-                             + ("; in bundle mode the primary passes' share of the floor is 0.35 cycles per sphere (one 6-flop test per "
-                                "(pixel, sphere) for the 64 samples of the pass, DESIGN.md 5.2d), weighted by primary_ray_fraction" if bundle else "")
-                             if pair_kernel else
-                             "15 of the 20 flops' instructions are mandatory separate roundings (parity), so 15 FP32 issue cycles/test "
-                             "is the hard floor: frac <= 20/30 = 0.667; see DESIGN.md"),
-        "kernel_ms": kms,
-        "traffic": None, "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
-    }
-    prof = os.path.join(ROOT, "profiles", "r1_roofline_traffic.json")
-    if os.path.exists(prof):
-        try:
-            with open(prof) as f:
-                roofline.update(json.load(f))
-        except (OSError, ValueError):
-            pass
+    spp_per_launch = SPP if bands else SPP // n_gpus
+    roofline = roofline_block(info0, n_pad, rays_per_launch, kms, expected_kernel(n_pad, spp_per_launch), peaks) if n_gpus == 1 else None
 
     # ---- HBM roofline of accumulate/tonemap standalone (A8-A9): resolve_sum_kernel -------------
     # 36 algorithmic bytes per pixel (16 R + 16 W accumulator, 4 W RGBA8); at N = 1 the
     # path kernel does this work itself, so the kernel is timed here on the step's own buffers.
     hbm = None
-    if not args.no_resolve_bench:
+    if not args.no_resolve_bench and n_gpus == 1:
         reps = 20
         for _ in range(3):
             b.resolve_sum(SPP)
@@ -383,15 +462,48 @@ def run_gpu_arm(args):
         r_ms = r0.elapsed_time(r1) / reps
         gbs = 36.0 * W * H / (r_ms * 1e-3) / 1e9
         peak_gbs = float(peaks.get("hbm_gbs", 6451.8))
-        hbm = {"bound": "hbm", "kernel": "resolve_sum_kernel (mean + tonemap + pack after the cross-GPU sum)", "achieved": gbs, "peak": peak_gbs,
+        hbm = {"bound": "hbm", "kernel": "resolve_sum_kernel (mean + tonemap + pack after the cross-GPU sum of the sample partition)", "achieved": gbs, "peak": peak_gbs,
                "unit": "GB/s", "frac": gbs / peak_gbs, "bytes_per_pixel": 36, "pixels": W * H, "launch_us": r_ms * 1e3, "launches": reps,
                "l2": f"working set {20 * W * H / 1e6:.0f} MB " + ("> 126 MB L2" if 20 * W * H > 126e6 else "fits the 126 MB L2: not an HBM number"),
                "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy bandwidth, burst)", "traffic": None}
 
+    # ---- the other BASELINE configs, one short run each, with the CPU reference's rate on the same scene -----------
+    others = None
+    if n_gpus == 1 and not args.no_workloads and args.workload == "synth1k_4k_256spp":
+        others = {}
+        gold = load_goldens()
+        for name in ("demo720_1spp", "demo1080_64spp", "stress64k_1080_16spp"):
+            si, w2, h2, spp2, d2 = WORKLOADS[name]
+            s2, sky2, _ = srt.host_scene(si)
+            cam2 = srt.host_camera(si, w2, h2)
+            b.set_scene(s2, sky2, LANE_WIDTH, FMA_DOT)
+            b.resize(w2, h2)
+            reps = 20 if name == "demo720_1spp" else 3
+            for _ in range(2):
+                b.render(cam2, 0, spp2); b.wait()
+            msl, rays2 = [], 0
+            for _ in range(reps):
+                b.render(cam2, 0, spp2)
+                m, rays2 = b.wait()
+                msl.append(m)
+            entry = {"description": d2, "spheres": int(len(s2)), "mrays_per_s": rays2 / float(np.median(msl)) / 1e3, "kernel_ms": float(np.median(msl)),
+                     "rays": int(rays2), "kernel": expected_kernel((len(s2) + 7) // 8 * 8, spp2), "launches": reps}
+            g = gold.get(PARITY_KEYS.get(name, ""))
+            if g is not None:
+                entry["parity_check"] = {"rgba_equal": sha(b.read_rgba8()) == g["rgba"], "accum_equal": sha(b.read_accum()) == g["accum"],
+                                         "rays_equal": int(rays2) == g["rays"], "against": "tests/golden/ref_full_hashes.json:" + PARITY_KEYS[name]}
+            if not args.no_cpu:
+                try:
+                    r = cpu_reference_run(srt, si, w2, h2, budget_s=3.0, probe_s=0.3)
+                    entry["cpu_reference"] = {"mrays_per_s": r["mrays"], "cores": r["cores"], "sample": r["sample"], "variant": r["variant"]}
+                    entry["gpu_over_cpu_rate"] = entry["mrays_per_s"] / r["mrays"]
+                except Exception as e:   # noqa: BLE001 - reported, never required
+                    entry["cpu_reference"] = {"unavailable": str(e)}
+            others[name] = entry
+
     # ---- secondary metric: ms/frame @1080p, progressive 1 spp/frame (BASELINE configs[3]) --------
     lat = None
     if n_gpus == 1 and not args.no_latency:
-        b.bind_device_buffers(None, None)
         s0, sky0, _ = srt.host_scene(0)
         cam0 = srt.host_camera(0, 1920, 1080)
         b.set_scene(s0, sky0, LANE_WIDTH, FMA_DOT)
@@ -405,17 +517,27 @@ def run_gpu_arm(args):
                 dev.append(ms); wall.append((time.perf_counter() - tw) * 1e3)
         lat = {"frames": len(dev), "device_ms_p50": float(np.percentile(dev, 50)), "device_ms_p99": float(np.percentile(dev, 99)),
                "wall_ms_p50": float(np.percentile(wall, 50)), "wall_ms_p99": float(np.percentile(wall, 99)),
-               "protocol": "BASELINE configs[3]: scene 0, 1920x1080, 1 spp/frame, 50 warm-up frames, exact running mean on device, read-back excluded"}
+               "host_overhead_ms_p50": float(np.percentile(np.array(wall) - np.array(dev), 50)),
+               "protocol": "BASELINE configs[3]: scene 0, 1920x1080, 1 spp/frame, 50 warm-up frames, exact running mean on device, read-back excluded; "
+                           "wall = srt_render + srt_wait through the ctypes binding (one kernel launch per frame: no memset, no copy, cached launch configuration)"}
 
     # ---- CPU baseline: the reference's own code on this box's host cores, bounded sample ---------
     cpu = None
     if n_gpus == 1 and not args.no_cpu:
         try:
             r = cpu_reference_run(srt, scene_idx, W, H, budget_s=args.cpu_seconds)
-            cpu = {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"], "variant": r["variant"]}
+            cpu = {"value": r["mrays"], "unit": "Mrays/s", "cores": r["cores"], "kind": "reference", "sample": r["sample"], "variant": r["variant"],
+                   "variant_rates_mrays": r["variant_rates_mrays"]}
         except Exception as e:   # noqa: BLE001 - the baseline is reported, never required
             cpu = {"value": None, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference", "sample": f"unavailable: {e}"}
 
+    if n_gpus == 1:
+        parallelism = "1 GPU (exact running mean)"
+    elif bands:
+        parallelism = (f"image partition x{n_gpus}: interleaved rows of 8x4 blocks, exact running mean per rank, srt_gather_rgba = one NCCL sum-reduce "
+                       f"of the RGBA8 words ({W * H * 4 / 1e6:.1f} MB) issued by libsrt_cuda.so; bit-identical to 1 GPU")
+    else:
+        parallelism = f"sample partition x{n_gpus}: SUM accumulators, srt_reduce_accum = NCCL sum-reduce ({W * H * 16 / 1e6:.1f} MB) issued by libsrt_cuda.so, resolve on rank 0"
     line = {
         "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": n_gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -423,24 +545,29 @@ def run_gpu_arm(args):
         "timing": "CUDA events on the launching stream around the K steps, max over ranks; wall clock of the same region in wall_ms_per_step",
         "wall_ms_per_step": wall_elapsed * 1e3 / args.steps,
         "config": {"workload": args.workload, "description": desc, "spheres": int(len(spheres)), "width": W, "height": H, "spp": SPP,
-                   "max_bounces": 5, "lane_width": LANE_WIDTH, "fma_dot": FMA_DOT,
-                   "parallelism": f"sample-sharded x{n_gpus}" + (" + NCCL reduce(sum) to rank 0" if n_gpus > 1 else " (exact running mean)"),
-                   "l2": (f"accumulator + RGBA8 working set {H * W * 20 / 1e6:.0f} MB" + (" > 126 MB L2" if H * W * 20 > 126e6 else " (fits L2)")
-                          + "; the step is FP32-issue-bound with the sphere tables in shared memory, HBM traffic is < 0.1 % of the "
-                            "step (ncu: dram 7 MB per 42 ms launch), so L2 residency cannot change the number")},
+                   "max_bounces": 5, "lane_width": LANE_WIDTH, "fma_dot": FMA_DOT, "partition": "bands" if bands else "samples",
+                   "parallelism": parallelism, "nccl": comm_info,
+                   "l2": (f"framebuffer working set {H * W * 20 / 1e6:.0f} MB" + (" > 126 MB L2" if H * W * 20 > 126e6 else " (fits L2)")
+                          + "; the step is bound by FP32 instruction issue with the sphere tables in shared memory, its DRAM traffic is in roofline.traffic")},
         "rays_per_step": rays_total / args.steps, "gpu_launches": int(launches_total),
+        "parity_check": parity,
         "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(spheres.nbytes + camera.nbytes),
                 "d2h_bytes_per_step": int(H * W * 4), "steps": e2e_steps, "ms_per_step": e2e_elapsed * 1e3 / e2e_steps,
-                "image_checksum": checksum},
-        "clocks": clocks, "roofline": roofline,
+                "rgba_equal_to_timed_steps": e2e_rgba_equal},
+        "clocks": clocks,
     }
+    if roofline is not None:
+        line["roofline"] = roofline
     if cpu is not None:
         line["cpu_baseline"] = cpu
     if hbm is not None:
         line["roofline_hbm"] = hbm
     if lat is not None:
         line["frame_latency_1080p"] = lat
+    if others is not None:
+        line["workloads"] = others
     print(json.dumps(line), file=_STDOUT, flush=True)
+    b.close()
     if dist is not None:
         dist.destroy_process_group()
     return 0
@@ -456,11 +583,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="synth1k_4k_256spp", choices=sorted(WORKLOADS))
+    ap.add_argument("--partition", default="bands", choices=["bands", "samples"], help="how N > 1 GPUs split a frame")
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="wall-time budget of the CPU baseline sample")
     ap.add_argument("--latency-frames", type=int, default=1000)
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-latency", action="store_true")
     ap.add_argument("--no-resolve-bench", action="store_true")
+    ap.add_argument("--no-workloads", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE JSON line: libraries that write to fd 1 (NCCL prints its version
     # banner there) are sent to stderr while the benchmark runs.
