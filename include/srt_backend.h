@@ -113,6 +113,21 @@ int srt_bind_device_buffers(srt_backend *b, void *accum_dev, void *rgba_dev);
 
 /* Kick one batch: the WorkQueueStart replacement. Asynchronous. */
 int srt_render(srt_backend *b, const srt_camera *camera, const srt_render_args *args);
+/* srt_render that allocates NOTHING (no cudaMalloc / cudaFree, no allocating library routine).  No counterpart in the
+ * reference: added for callers that cannot allocate -- code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc.  The one piece of scratch memory the render kernels
+ * need on the fly (the pool kernel's per-pixel chunk counters) lives in a file-scope device array of
+ * SRT_STATIC_MAX_PIXELS x 4 bytes = 8 MiB that every GPU loading the library holds until the process exits.
+ *   - images of more than SRT_STATIC_MAX_PIXELS pixels are rejected with SRT_ERR_TOO_LARGE (use srt_render);
+ *   - record_primary is rejected (its buffers are allocated by srt_render);
+ *   - same kernels and bit-identical buffers as srt_render; launches that srt_render runs in bundle mode (staging
+ *     rows it allocates) run the plain pool kernel here, so large scenes at >= 8 samples per call are slower;
+ *   - the array is shared by every handle and call on a device and keeps the last call's contents: the part a
+ *     launch reads is reset on the handle's stream first, and calls that OVERLAP on the GPU (several handles of
+ *     one device rendering at once) race -- serialise them.
+ * srt_set_scene / srt_resize (which do allocate) must have been called before, as for srt_render. */
+#define SRT_STATIC_MAX_PIXELS (2u << 20)
+int srt_render_static(srt_backend *b, const srt_camera *camera, const srt_render_args *args);
 /* 1 = finished, 0 = still running (WorkQueueHasCompleted). */
 int srt_poll(srt_backend *b);
 /* Block until finished (WorkQueueWaitUntilCompletion); out_ms = device time of the last

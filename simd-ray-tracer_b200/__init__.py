@@ -39,7 +39,9 @@ EXPORTS = [
     "srt_filter_audit", "srt_write_accum", "srt_device_kat",
     "srt_comm_unique_id", "srt_comm_init_rank", "srt_comm_destroy", "srt_comm_info", "srt_set_partition",
     "srt_reduce_accum", "srt_gather_rgba", "srt_gather_accum", "srt_comm_group_begin", "srt_comm_group_end",
+    "srt_render_static",
 ]
+STATIC_MAX_PIXELS = 2 << 20
 COMM_ID_BYTES = 128
 KAT_PCG, KAT_RANDOM_FLOAT, KAT_STREAM_SEED, KAT_NORMALIZE, KAT_REFLECTANCE, KAT_LINEAR_TO_SRGB, KAT_PACK = range(7)
 _KAT_IO = {  # op: (input dtype, values per record in, output dtype, values per record out)
@@ -87,6 +89,7 @@ def load_library():
     L.srt_reset_accumulation.argtypes = [vp]
     L.srt_bind_device_buffers.argtypes = [vp, vp, vp]
     L.srt_render.argtypes = [vp, vp, C.POINTER(RenderArgs)]
+    L.srt_render_static.argtypes = [vp, vp, C.POINTER(RenderArgs)]
     L.srt_poll.argtypes = [vp]
     L.srt_wait.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]
     L.srt_resolve_sum.argtypes = [vp, C.c_uint32]
@@ -159,6 +162,12 @@ class Backend:
         cam = np.ascontiguousarray(camera)
         args = RenderArgs(first_sample, n_samples, stride, mode, stream_base, int(record_primary), 0)
         self._check(self.L.srt_render(self.h, cam.ctypes.data, C.byref(args)))
+
+    def render_static(self, camera, first_sample=0, n_samples=1, stride=1, mode=ACCUM_MEAN, stream_base=0):
+        """srt_render_static: the render that allocates nothing (scratch in a file-scope device array)."""
+        cam = np.ascontiguousarray(camera)
+        args = RenderArgs(first_sample, n_samples, stride, mode, stream_base, 0, 0)
+        self._check(self.L.srt_render_static(self.h, cam.ctypes.data, C.byref(args)))
 
     def poll(self):
         return self._check(self.L.srt_poll(self.h)) == 1

@@ -19,6 +19,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -847,6 +848,7 @@ struct srt_backend {
     unsigned char *d_counters = nullptr;
     bool counters_dirty = true;          // first launch, or a failed one: memset before the next launch
     uint32_t *d_done = nullptr;          // pool kernel: per-pixel chunk counters (KernelParams::done)
+    uint32_t *d_static_done = nullptr;   // device address of the file-scope scratch of srt_render_static (resolve_static_scratch)
     uint32_t pool_seq = 0;               // pool launches issued: done-tag sequence (20 bits, 0xFFFFF reserved for the 0xFF fill)
     int slab_axis = 1;                   // axis contained in the slab planes: least spread of the centres
     double omax_scene = 0.0;             // >= |C| + r of every sphere (bound on secondary-ray origins)
@@ -993,6 +995,30 @@ extern "C" {
 
 const char *srt_last_error(const srt_backend *b) { return b ? b->err.c_str() : g_create_error.c_str(); }
 
+// ---- srt_render_static: scratch without cudaMalloc ----------------------------------------------------------
+// The pool kernel's per-pixel chunk counters (KernelParams::done) are scratch memory that srt_render allocates on its
+// first pool launch.  Callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+// that forbid it) use srt_render_static, whose scratch is this file-scope array: kStaticDonePixels x 4 B = 8 MiB, held by
+// every GPU that loads the library until the process exits.  In HOST code `g_static_done` is only a stand-in for the
+// symbol, not a device address: the address is taken once per device with cudaGetSymbolAddress (that device current) and
+// that pointer is what the kernel gets.
+constexpr uint32_t kStaticDonePixels = 2u << 20;             // 2,097,152 pixels: up to 1920 x 1080 (and 2048 x 1024)
+static __device__ __align__(256) uint32_t g_static_done[kStaticDonePixels];
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_static_mu;
+static uint32_t *g_static_done_ptr[kStaticMaxDevices];       // device address of g_static_done on each device, once resolved
+static int resolve_static_scratch(srt_backend *b) {          // the caller has made b->device current
+    if (b->device < 0 || b->device >= kStaticMaxDevices) return SRT_OK;     // srt_render_static will refuse; everything else works
+    std::lock_guard<std::mutex> lock(g_static_mu);
+    if (!g_static_done_ptr[b->device]) {
+        uint32_t *ptr = nullptr;
+        SRT_CUDA(b, cudaGetSymbolAddress((void **)&ptr, g_static_done));
+        g_static_done_ptr[b->device] = ptr;
+    }
+    b->d_static_done = g_static_done_ptr[b->device];
+    return SRT_OK;
+}
+
 static int create_resources(srt_backend *b) {
     SRT_CUDA(b, cudaSetDevice(b->device));
     SRT_CUDA(b, cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking));
@@ -1003,6 +1029,10 @@ static int create_resources(srt_backend *b) {
     SRT_CUDA(b, cudaHostAlloc(&b->h_rays, 2 * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
     b->h_rays[0] = 0;                    // [0] rays of the last launch, [1] spin-limit report of the debug build
     b->h_rays[1] = 0;
+    {
+        const int rc = resolve_static_scratch(b);            // set-up of srt_render_static: once per device, this device current
+        if (rc != SRT_OK) return rc;
+    }
 #ifdef SRT_SPIN_LIMIT
     {
         unsigned long long *report = b->h_rays + 1;
@@ -1489,6 +1519,98 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
         fprintf(stderr, "[srt pool] acquire spins: steady %llu, tail %llu; primary passes: bundled %llu, per-ray %llu, pixel runs %llu, lane-0 waits %llu\n",
                 dbg[0], dbg[1], dbg[2], dbg[3], dbg[4], dbg[5]);
     }
+    return SRT_OK;
+}
+
+// srt_render without any allocation: the pool kernel's chunk counters live in the file-scope array g_static_done.
+// Same kernels, same results as srt_render (bundle mode needs staging rows that only srt_render allocates, so launches
+// that srt_render would run in bundle mode run the non-bundle pool kernel here -- bit-identical by construction, slower).
+// The array is shared by every handle and every call on the device and keeps the last call's contents: the part this
+// launch reads is reset on the stream first; calls that overlap on the GPU (two handles of one device) race.
+int srt_render_static(srt_backend *b, const srt_camera *cam, const srt_render_args *args) {
+    if (!b) return SRT_ERR_INVALID;
+    KernelParams P;
+    int rc = make_params(b, cam, args, "srt_render_static", P);
+    if (rc) return rc;
+    if (args->record_primary) return fail(b, SRT_ERR_INVALID, "srt_render_static: record_primary needs buffers that only srt_render allocates");
+    const uint64_t n_pixels = (uint64_t)b->width * b->height;
+    if (n_pixels > kStaticDonePixels)
+        return fail(b, SRT_ERR_TOO_LARGE, "srt_render_static: image of " + std::to_string(n_pixels) + " pixels exceeds the static scratch of " +
+                                          std::to_string(kStaticDonePixels) + " pixels (SRT_STATIC_MAX_PIXELS); use srt_render");
+    if (!b->d_static_done) return fail(b, SRT_ERR_INVALID, "srt_render_static: static scratch was not resolved for this device");
+    SRT_CUDA(b, cudaSetDevice(b->device));
+    rc = drain(b);
+    if (rc) return rc;
+    b->gathered_rgba = b->gathered_accum = false;
+    if (P.total_items == 0u) {
+        *b->h_rays = 0;
+        b->events_recorded = false;
+        return SRT_OK;
+    }
+    const Knobs &K = b->knobs;
+    int pool_threads = 0;
+    for (int t : kPoolResidentThreads) {
+        if (K.pool_threads && K.pool_threads != t) continue;
+        if (b->n_pad <= (uint32_t)kPairsMaxSpheres && pool_smem_bytes(b->n_pad, t, false) <= b->max_smem_optin) { pool_threads = t; break; }
+    }
+    const bool pool = K.variant == 9 || K.variant == 12 || (K.variant == 0 && b->n_pad >= kPoolMinSpheres);
+    const bool stream = pool && (K.variant == 12 || pool_threads == 0);
+    const bool packed = !pool && K.variant != 1 && b->opt.lane_width != 1 && b->n_pad > 16u;
+    if (!pool && (size_t)b->n_pad * sizeof(float4) > b->max_smem_optin)
+        return fail(b, SRT_ERR_TOO_LARGE, "srt_render_static: scene too large for the one-path kernel");
+    if (packed) P.spheres = b->d_spheres2;
+    P.debug = nullptr;
+    if (pool) {
+        uint32_t chunk = K.pool_chunk ? K.pool_chunk : kPoolChunkSamples;
+        const uint32_t max_chunks = std::min<uint32_t>(4095u, 0xF0000000u / P.items_per_gen);
+        if ((args->n_samples + chunk - 1) / chunk > max_chunks) chunk = (args->n_samples + max_chunks - 1) / max_chunks;
+        const uint32_t n_chunks = (args->n_samples + chunk - 1) / chunk;
+        P.chunk_span = chunk * args->sample_stride;
+        P.total_items = P.items_per_gen * n_chunks;
+        P.n_chunks = n_chunks;
+        // The counters of this image's pixels must not match this launch's tag: other handles and earlier calls wrote the
+        // array with tags of their own, so it is reset (0xFF: the reserved tag) before every launch that reads it.
+        if (n_chunks > 1u) SRT_CUDA(b, cudaMemsetAsync(b->d_static_done, 0xFF, (size_t)n_pixels * sizeof(uint32_t), b->stream));
+        const uint32_t tag = b->pool_seq % 0xFFFFFu;
+        b->pool_seq = tag + 1u;
+        P.done = b->d_static_done;
+        P.done_tag = tag << 12;
+    }
+    if (stream) pool_threads = kPoolThreads;
+    render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, false) : pick_kernel(b->opt, packed);
+    if (!kernel) return fail(b, SRT_ERR_INVALID, "srt_render_static: this build (SRT_FAST_BUILD) only carries the lane_width 8 + FMA kernels");
+    const int threads = pool ? pool_threads : kBlockThreads;
+    const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream, false) : (size_t)b->n_pad * sizeof(float4);
+    int carve = -1;
+    if (pool) {
+        const size_t ctas = stream ? kPoolMinBlocks : 1;
+        carve = (int)std::min<size_t>(100, (ctas * (smem + 1024) * 100 + 228 * 1024 - 1) / (228 * 1024));
+    }
+    int per_sm = 0;
+    rc = launch_cfg(b, kernel, threads, smem, carve, &per_sm);
+    if (rc) return rc;
+    uint32_t grid = (uint32_t)(b->sm_count * per_sm);
+    const uint32_t paths_per_block = pool ? 64u * (threads / 32 + kPoolSpareBatches) : (uint32_t)threads;
+    const uint32_t max_useful = (P.total_items + paths_per_block - 1) / paths_per_block;
+    if (grid > max_useful) grid = max_useful;
+    if (b->counters_dirty) {
+        SRT_CUDA(b, cudaMemsetAsync(b->d_counters, 0, 64, b->stream));
+        b->counters_dirty = false;
+    }
+    SRT_CUDA(b, cudaEventRecord(b->ev_start, b->stream));
+    if (stream) {
+        P.ptab = b->d_ptab;
+        build_slab_kernel<<<(b->n_pad + 255) / 256, 256, 0, b->stream>>>(b->d_scan, b->d_spheres, (float *)b->d_ptab, b->n_pad, b->n_spheres,
+                                                                        P.slab_axis, P.omax);
+        b->launches += 1;
+    }
+    kernel<<<grid, threads, smem, b->stream>>>(P);
+    const cudaError_t le = cudaGetLastError();
+    if (le != cudaSuccess) { b->counters_dirty = true; return fail(b, SRT_ERR_CUDA, std::string("srt_render_static: launch: ") + cudaGetErrorString(le)); }
+    SRT_CUDA(b, cudaEventRecord(b->ev_stop, b->stream));
+    b->events_recorded = true;
+    b->launches += 1;
+    b->in_flight = true;
     return SRT_OK;
 }
 
