@@ -224,6 +224,7 @@ class Backend:
 
     # ---- several devices (one handle per device / process) --------------------------------
     def comm_init_rank(self, n_ranks, rank, unique_id):
+        _preload_nccl()
         buf = np.frombuffer(bytes(unique_id), np.uint8).copy()
         assert buf.nbytes == COMM_ID_BYTES
         self._check(self.L.srt_comm_init_rank(self.h, n_ranks, rank, buf.ctypes.data))
@@ -232,6 +233,7 @@ class Backend:
         self._check(self.L.srt_comm_destroy(self.h))
 
     def comm_info(self):
+        _preload_nccl()
         r, n, v = C.c_int(), C.c_int(), C.c_int()
         self._check(self.L.srt_comm_info(self.h, C.byref(r), C.byref(n), C.byref(v)))
         return dict(rank=r.value, n_ranks=n.value, nccl_version=v.value)
@@ -266,8 +268,35 @@ class Backend:
         return self.L.srt_cuda_stream(self.h)
 
 
+_nccl_preloaded = False
+
+
+def _preload_nccl():
+    """libsrt_cuda.so binds NCCL at run time: the libnccl.so.2 already mapped into the process, else the loader's.  In a
+    Python process PyTorch may be imported LATER and needs its own (newer) bundled libnccl.so.2 -- glibc would hand it the
+    one already loaded under that soname.  So before the library's first NCCL call, map the bundled one if there is one."""
+    global _nccl_preloaded
+    if _nccl_preloaded:
+        return
+    _nccl_preloaded = True
+    import importlib.util
+    import sys
+    if "torch" in sys.modules:
+        return                                   # torch's NCCL is already in the process
+    try:
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(d, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                C.CDLL(path, mode=C.RTLD_GLOBAL)
+                return
+    except (ImportError, OSError, ValueError):
+        pass
+
+
 def comm_unique_id():
     """128-byte NCCL unique id (made by one rank, handed to every rank's Backend.comm_init_rank)."""
+    _preload_nccl()
     L = load_library()
     buf = np.zeros(COMM_ID_BYTES, np.uint8)
     rc = L.srt_comm_unique_id(buf.ctypes.data)
