@@ -54,7 +54,9 @@ static void Usage() {
             "  --pfm writes the linear accumulator as a PFM image.\n"
             "  --gpus N: devices D .. D+N-1 render interleaved rows of 8x4 blocks of every frame and worker 0 gathers them (NCCL);\n"
             "  the image is bit-identical for every N.  --threads is render_params.ThreadCount: workers used per frame (0 = all).\n"
-            "  --spf: samples per OnRender frame (reference: 1).  --orbit: hold key A for FRAMES frames first.\n");
+            "  --spf: samples per OnRender frame (reference: 1).  --orbit: hold key A for FRAMES frames first.\n"
+            "  --latency FRAMES: after the render, time FRAMES bare kicks (srt_render + srt_wait, --spf samples each, no read-back):\n"
+            "  device and wall p50 / p99 per frame (BASELINE configs[3] measured from C++, without the Python binding).\n");
 }
 
 int main(int argc, char **argv) {
@@ -62,7 +64,7 @@ int main(int argc, char **argv) {
     bool Simd = true;
     backend_params BP;
     const char *Out = nullptr, *AccumOut = nullptr, *SceneFile = nullptr, *DumpScene = nullptr, *CkptOut = nullptr, *CkptIn = nullptr, *PfmOut = nullptr;
-    u32 ThreadCount = 0;
+    u32 ThreadCount = 0, LatencyFrames = 0;
     for (int i = 1; i < argc; ++i) {
         std::string A = argv[i];
         auto Next = [&]() -> const char * { if (i + 1 >= argc) { Usage(); exit(2); } return argv[++i]; };
@@ -86,6 +88,7 @@ int main(int argc, char **argv) {
         else if (A == "--resume") CkptIn = Next();
         else if (A == "--pfm") PfmOut = Next();
         else if (A == "--threads") ThreadCount = atoi(Next());
+        else if (A == "--latency") LatencyFrames = atoi(Next());
         else { Usage(); return 2; }
     }
     if (Spf == 0) Spf = 1;
@@ -175,14 +178,42 @@ int main(int argc, char **argv) {
         fwrite(Acc.data(), sizeof(f32), Acc.size(), F);
         fclose(F);
     }
+    // The bare kick of BASELINE configs[3]: what replaces WorkQueueStart + WorkQueueWaitUntilCompletion (main.cpp:852, base.h:175),
+    // timed from C++: wall = srt_render + srt_wait, device = CUDA events around the kernel.
+    f64 LatDevP50 = 0, LatDevP99 = 0, LatWallP50 = 0, LatWallP99 = 0, LatOverP50 = 0;
+    if (LatencyFrames && GetDeviceCount() == 1) {
+        const scene *Sc = GetScene(Scene);
+        srt_camera Cam;
+        ComputeCamera(*Sc, Sc->DefaultDistanceFromLookAt, Sc->DefaultXAngle, Sc->DefaultYHeight, W, H, &Cam);
+        srt_render_args Args = {};
+        Args.n_samples = Spf; Args.sample_stride = 1; Args.accum_mode = SRT_ACCUM_MEAN; Args.stream_base = BP.StreamBase;
+        std::vector<f64> Dev, Wal, Over;
+        u32 Sample = GetAccumulatedSampleCount();
+        for (u32 f = 0; f < LatencyFrames + 50; ++f, Sample += Spf) {
+            Args.first_sample = Sample;
+            const f64 T0 = QueryTimestampInMilliseconds();
+            f64 FrameDev = 0;
+            if (srt_render(GetBackend(), &Cam, &Args) != SRT_OK || srt_wait(GetBackend(), &FrameDev, nullptr) != SRT_OK) {
+                fprintf(stderr, "latency loop failed: %s\n", srt_last_error(GetBackend()));
+                return 1;
+            }
+            const f64 T1 = QueryTimestampInMilliseconds();
+            if (f >= 50) { Dev.push_back(FrameDev); Wal.push_back(T1 - T0); Over.push_back(T1 - T0 - FrameDev); }
+        }
+        auto Pct = [](std::vector<f64> &V, f64 P) { std::sort(V.begin(), V.end()); return V[std::min(V.size() - 1, (size_t)(V.size() * P))]; };
+        LatDevP50 = Pct(Dev, 0.5); LatDevP99 = Pct(Dev, 0.99); LatWallP50 = Pct(Wal, 0.5); LatWallP99 = Pct(Wal, 0.99); LatOverP50 = Pct(Over, 0.5);
+    }
     std::sort(FrameMs.begin(), FrameMs.end());
     const f64 P50 = FrameMs[FrameMs.size() / 2], P99 = FrameMs[std::min(FrameMs.size() - 1, (size_t)(FrameMs.size() * 0.99))];
     const scene *S = GetScene(Scene);
     printf("{\"scene\": \"%s\", \"spheres\": %u, \"width\": %u, \"height\": %u, \"spp\": %u, \"frames\": %zu, "
            "\"rays\": %llu, \"device_ms\": %.4f, \"wall_ms\": %.3f, \"mrays_per_s\": %.2f, "
-           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u, \"resumed_from\": %u, \"gpus\": %u}\n",
+           "\"frame_ms_p50\": %.4f, \"frame_ms_p99\": %.4f, \"samples_accumulated\": %u, \"resumed_from\": %u, \"gpus\": %u, "
+           "\"latency_frames\": %u, \"latency_device_ms_p50\": %.5f, \"latency_device_ms_p99\": %.5f, \"latency_wall_ms_p50\": %.5f, "
+           "\"latency_wall_ms_p99\": %.5f, \"latency_host_overhead_ms_p50\": %.5f}\n",
            S->Name, S->SphereCount, W, H, Frames * Spf, FrameMs.size(), (unsigned long long)TotalRays, TotalMs, Wall,
-           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount(), ResumedSamples, GetDeviceCount());
+           TotalMs > 0 ? TotalRays / TotalMs / 1e3 : 0.0, P50, P99, GetAccumulatedSampleCount(), ResumedSamples, GetDeviceCount(),
+           LatencyFrames, LatDevP50, LatDevP99, LatWallP50, LatWallP99, LatOverP50);
     OnShutdown();
     return 0;
 }
