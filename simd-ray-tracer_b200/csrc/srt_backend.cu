@@ -304,6 +304,7 @@ render_pool(const __grid_constant__ KernelParams P) {
             ctl->head[1] = 0; ctl->tail[1] = 0; ctl->avail[1] = 0;
             ctl->head[2] = 0; ctl->tail[2] = 0; ctl->avail[2] = 0;
             ctl->inflight = 0; ctl->retired = 0; ctl->spins_steady = 0; ctl->spins_tail = 0;
+            ctl->scanning[0] = ctl->scanning[1] = ctl->scanning[2] = ctl->scanning[3] = 0;
         }
     }
     __syncthreads();
@@ -535,14 +536,18 @@ render_pool(const __grid_constant__ KernelParams P) {
                                                rays, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
                 } else {
                     const SlabRays sr = make_slab_rays(P.slab_axis, ox, oy, oz, dx, dy, dz, P.omax2);
+                    if (BUNDLE && kScanTarget && lane == 0) atomicAdd(&ctl->scanning[(tid >> 5) & 3u], 1u);
                     stream_pass<W, FMA>(ws, P.ptab, P.scan_table, P.spheres, P.n_pad, P.n_spheres, sr, rays, lane, ox, oy, oz, dx, dy, dz, P.neg_one, P.one, b0, b1);
+                    if (BUNDLE && kScanTarget && lane == 0) atomicSub(&ctl->scanning[(tid >> 5) & 3u], 1u);
                 }
             } else {
                 if (BUNDLE && use_bundle) {
                     bundle_scan<false>(s_slab, 0u, P.n_pad, P.cam.pos[ip], P.cam.pos[iq], heads0, heads1, bp0, bp1, lane, queue, qn);
                 } else {
                     const SlabRays sr = make_slab_rays(P.slab_axis, ox, oy, oz, dx, dy, dz, P.omax2);
+                    if (BUNDLE && kScanTarget && lane == 0) atomicAdd(&ctl->scanning[(tid >> 5) & 3u], 1u);
                     scan_slab_tile(s_slab, P.n_pad, 0u, sr, queue, qn);
+                    if (BUNDLE && kScanTarget && lane == 0) atomicSub(&ctl->scanning[(tid >> 5) & 3u], 1u);
                 }
                 const ScanRays rays = make_scan_rays(ox, oy, oz, dx, dy, dz);
                 const FetchScanResident fetch_scan = {s_scan};

@@ -39,6 +39,7 @@ struct PoolCtl {
     unsigned int inflight;                     // warps currently holding a batch
     unsigned int retired;                      // slots that ran out of work
     unsigned int spins_steady, spins_tail;     // diagnostics: acquire-loop iterations before / after work ran out
+    unsigned int scanning[4];                  // warps of each SM sub-partition (warp id % 4) that are inside a per-ray slab scan
 };
 
 // Inline on purpose: an out-of-line copy (one instead of seven in pool_acquire) measured 6 % slower.
@@ -66,9 +67,23 @@ __device__ __forceinline__ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want
 #endif
 constexpr uint32_t kFoldBatchMin = SRT_FOLD_MIN;   // ring F entries that make a fold pass worth a warp's while (two chunks per lane; 64 beats 32 and 16 by 1 %)
 
+#ifndef SRT_SCAN_TARGET
+#define SRT_SCAN_TARGET 3
+#endif
+// Bundle-mode kernels: scanning warps an SM sub-partition wants; below it, a warp takes secondary rays first (0: off).
+// Measured on the 4K / 256-spp launch: 0: 711.8 ms, 1: 705.1, 2: 693.3, 3: 684.5, 4: 688.8, 5: 687.5, always: 687.7.
+constexpr uint32_t kScanTarget = SRT_SCAN_TARGET;
+
 template <bool FOLD = false>
 __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, bool hungry, uint32_t &kind, uint32_t &n, uint32_t &pos) {
     n = 0; kind = 0; pos = 0;
+    // Only the per-ray slab scan keeps the issue port busy; refine / select / shade and the bundled primary passes are
+    // latency-bound.  A sub-partition whose warps are all in those phases idles (18 % of the scheduler cycles before this),
+    // so a warp that finds fewer than kScanTarget scanning warps on its sub-partition takes a batch of secondary rays
+    // (= a scan) before anything else.  Bundle mode only: without it every pass scans (-3 % on the 256-sphere scene).
+    if (FOLD && kScanTarget && !hungry && *(volatile unsigned int *)&ctl->scanning[(threadIdx.x >> 5) & 3u] < kScanTarget) {
+        if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }
+    }
     if (hungry) {
         __nanosleep(200);
         if (FOLD && pool_try_take(ctl, 2, 1u, n, pos)) { kind = 2; return; }   // the chunk being waited for may sit in ring F
