@@ -7,10 +7,11 @@
 //
 // libnccl is NOT a link-time dependency of libsrt_cuda.so: a single-GPU user never needs it, and a process that
 // already carries an NCCL (PyTorch bundles its own libnccl.so.2) must keep using that one.  The library already
-// mapped into the process is preferred (RTLD_NOLOAD), then the loader's search path.  Without NCCL the srt_comm_*
-// calls fail with SRT_ERR_COMM and a message; nothing falls back to a host copy.
+// mapped into the process is preferred (RTLD_NOLOAD), then the loader's search path; SRT_NCCL_LIB=<path> names one
+// explicitly.  Without NCCL the srt_comm_* calls fail with SRT_ERR_COMM and a message; nothing falls back to a host copy.
 #pragma once
 #include <dlfcn.h>
+#include <cstdlib>
 #include <nccl.h>
 
 #include <mutex>
@@ -37,10 +38,15 @@ inline NcclApi &nccl_api() {
     static std::once_flag once;
     std::call_once(once, [] {
         const char *names[] = {"libnccl.so.2", "libnccl.so"};
-        for (const char *n : names) { api.handle = dlopen(n, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL); if (api.handle) break; }
+        if (const char *forced = getenv("SRT_NCCL_LIB")) {            // an explicit library path: nothing else is tried
+            api.handle = dlopen(forced, RTLD_NOW | RTLD_GLOBAL);
+            if (!api.handle) { const char *e = dlerror(); api.error = std::string("SRT_NCCL_LIB=") + forced + " cannot be loaded: " + (e ? e : "?"); return; }
+        }
+        if (!api.handle)
+            for (const char *n : names) { api.handle = dlopen(n, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL); if (api.handle) break; }
         if (!api.handle)
             for (const char *n : names) { api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL); if (api.handle) break; }
-        if (!api.handle) { api.error = std::string("libnccl.so.2 not found: ") + dlerror(); return; }
+        if (!api.handle) { const char *e = dlerror(); api.error = std::string("libnccl.so.2 not found: ") + (e ? e : "?"); return; }
         auto sym = [&](const char *name) -> void * {
             void *p = dlsym(api.handle, name);
             if (!p && api.error.empty()) api.error = std::string("libnccl: missing symbol ") + name;

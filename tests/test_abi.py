@@ -48,3 +48,26 @@ def test_product_never_touches_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
                 txt = open(os.path.join(dp, f), errors="ignore").read()
                 assert "liborc" not in txt and "srt_oracle" not in txt and "orclib" not in txt and "_ref/" not in txt, f
+
+
+def test_comm_calls_fail_loudly_without_nccl():
+    """The multi-device entry points bind NCCL at run time; when it cannot be loaded they return SRT_ERR_COMM (-5) with a
+    message -- no host-copy fallback.  (A fresh process: the binding caches the first dlopen.)"""
+    import subprocess
+    import sys
+    code = (
+        "import ctypes as C, os, sys\n"
+        "os.environ['SRT_NCCL_LIB'] = '/nonexistent/libnccl.so.2'\n"
+        f"L = C.CDLL({os.path.join(ROOT, 'simd-ray-tracer_b200', 'libsrt_cuda.so')!r})\n"
+        "L.srt_last_error.restype = C.c_char_p\n"
+        "L.srt_last_error.argtypes = [C.c_void_p]\n"
+        "buf = (C.c_ubyte * 128)()\n"
+        "rc = L.srt_comm_unique_id(buf)\n"
+        "print(rc, L.srt_last_error(None).decode())\n"
+        "rc2 = L.srt_comm_group_begin()\n"
+        "print(rc2)\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    lines = r.stdout.strip().splitlines()
+    assert lines[0].startswith("-5 ") and "SRT_NCCL_LIB" in lines[0] and "cannot be loaded" in lines[0]
+    assert lines[1] == "-5"
