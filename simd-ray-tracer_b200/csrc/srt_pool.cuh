@@ -74,32 +74,49 @@ constexpr uint32_t kFoldBatchMin = SRT_FOLD_MIN;   // ring F entries that make a
 // Measured on the 4K / 256-spp launch: 0: 711.8 ms, 1: 705.1, 2: 693.3, 3: 684.5, 4: 688.8, 5: 687.5, always: 687.7.
 constexpr uint32_t kScanTarget = SRT_SCAN_TARGET;
 
+// An attempt = take >= min entries of ring q, one byte: 0x80 | q | code << 2 (code 0: min 1, 1: min 64, 2: min kFoldBatchMin).
+// pool_acquire walks a list of attempts (one byte each, lowest byte first) with ONE inlined copy of pool_try_take: the
+// nine copies of the unrolled version were 2 KB of a hot code footprint that sits right at the 32 KB of the L1.5
+// instruction cache (12 % of the kernel's stall samples are instruction fetches).
+__device__ __forceinline__ constexpr uint64_t pool_attempt(int q, int code) { return 0x80u | (unsigned)q | ((unsigned)code << 2); }
+
 template <bool FOLD = false>
 __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, bool hungry, uint32_t &kind, uint32_t &n, uint32_t &pos) {
     n = 0; kind = 0; pos = 0;
+    constexpr uint64_t kSteady = FOLD ? (pool_attempt(2, 2) | pool_attempt(0, 1) << 8 | pool_attempt(1, 1) << 16)   // enough chunks to fold, one per lane; then P, then S
+                                      : (pool_attempt(0, 1) | pool_attempt(1, 1) << 8);
+    constexpr uint64_t kDrain = FOLD ? (pool_attempt(2, 0) | pool_attempt(1, 0) << 8 | pool_attempt(0, 0) << 16)
+                                     : (pool_attempt(1, 0) | pool_attempt(0, 0) << 8);
+    constexpr int kSteadyBits = FOLD ? 24 : 16;
     // Only the per-ray slab scan keeps the issue port busy; refine / select / shade and the bundled primary passes are
     // latency-bound.  A sub-partition whose warps are all in those phases idles (18 % of the scheduler cycles before this),
     // so a warp that finds fewer than kScanTarget scanning warps on its sub-partition takes a batch of secondary rays
     // (= a scan) before anything else.  Bundle mode only: without it every pass scans (-3 % on the 256-sphere scene).
+    uint64_t head = 0;                                    // one-shot attempts in front of the steady list
+    int head_bits = 0;
     if (FOLD && kScanTarget && !hungry && *(volatile unsigned int *)&ctl->scanning[(threadIdx.x >> 5) & 3u] < kScanTarget) {
-        if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }
+        head = pool_attempt(1, 1); head_bits = 8;
     }
-    if (hungry) {
+    if (hungry) {                                         // the chunk being waited for may sit in ring F; else advance any secondary ray
         __nanosleep(200);
-        if (FOLD && pool_try_take(ctl, 2, 1u, n, pos)) { kind = 2; return; }   // the chunk being waited for may sit in ring F
-        if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
+        head = FOLD ? (pool_attempt(2, 0) | pool_attempt(1, 0) << 8) : pool_attempt(1, 0);
+        head_bits = FOLD ? 16 : 8;
     }
     [[maybe_unused]] uint32_t spins = 0;
     for (;;) {
-        if (FOLD && pool_try_take(ctl, 2, kFoldBatchMin, n, pos)) { kind = 2; return; }  // enough chunks to fold, one per lane
-        if (pool_try_take(ctl, 0, 64u, n, pos)) { kind = 0; return; }
-        if (pool_try_take(ctl, 1, 64u, n, pos)) { kind = 1; return; }
-        if (*(volatile unsigned int *)&ctl->inflight == 0u) {            // nobody will add to the rings: drain partial batches
-            if (FOLD && pool_try_take(ctl, 2, 1u, n, pos)) { kind = 2; return; }
-            if (pool_try_take(ctl, 1, 1u, n, pos)) { kind = 1; return; }
-            if (pool_try_take(ctl, 0, 1u, n, pos)) { kind = 0; return; }
-            if (*(volatile unsigned int *)&ctl->retired == n_slots) return;
+        const bool quiet = *(volatile unsigned int *)&ctl->inflight == 0u;   // nobody will add to the rings: drain partial batches too
+        uint64_t list = head | (kSteady << head_bits);
+        if (quiet) list |= kDrain << (head_bits + kSteadyBits);
+        head = 0; head_bits = 0;
+#pragma unroll 1
+        while (list) {
+            const uint32_t a = (uint32_t)list & 0xFFu;
+            list >>= 8;
+            const int q = (int)(a & 3u);
+            const uint32_t code = (a >> 2) & 3u;
+            if (pool_try_take(ctl, q, code == 0u ? 1u : (code == 1u ? 64u : kFoldBatchMin), n, pos)) { kind = (uint32_t)q; return; }
         }
+        if (quiet && *(volatile unsigned int *)&ctl->retired == n_slots) return;
         if (*(volatile unsigned int *)&ctl->retired) ctl->spins_tail += 1; else ctl->spins_steady += 1;   // racy, diagnostic only
         __nanosleep(100);
         SRT_SPIN(kSpinAcquire, spins);
