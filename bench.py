@@ -203,16 +203,6 @@ def run_reference_arm(args):
 # ---------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------
-def expected_kernel(n_pad, spp_per_launch):
-    """Name of the kernel srt_render picks for the AVX2 profile (csrc/srt_backend.cu: srt_render, plan_bundle)."""
-    if n_pad < 64:
-        return "render_paths<8, 1, 0, 4, 4>" if n_pad <= 16 else "render_paths<8, 1, 1, 4, 3>"
-    bundle = 1 if (n_pad >= 384 and spp_per_launch >= 8 and os.environ.get("SRT_BUNDLE", "1") != "0") else 0
-    if n_pad > 8192:
-        return f"render_pool<8, 1, 256, 2, 1, {bundle}>"
-    return f"render_pool<8, 1, 896, 1, 0, {bundle}>"
-
-
 def roofline_block(info, n_pad, rays_per_launch, kms, kernel_name, peaks):
     """FP32 roofline of the dominant kernel.  `frac` is MEASURED: the FMA-pipe utilisation ncu reports for this very
     launch (profiles/r2_roofline_bench.json, produced by scripts/merge_roofline.py from the committed ncu CSV); it is
@@ -311,6 +301,7 @@ def run_gpu_arm(args):
         torch.cuda.synchronize()
 
     kernel_ms, kernel_rays = [], []
+    step_kernel = [""]
 
     def step():
         """One complete render of the workload, inputs resident in HBM."""
@@ -327,6 +318,7 @@ def run_gpu_arm(args):
         ms, rays = b.wait()
         kernel_ms.append(ms)
         kernel_rays.append(rays)
+        step_kernel[0] = b.last_kernel()          # the kernel the library launched (srt_last_kernel), not a guess
         return rays
 
     for _ in range(args.warmup):
@@ -441,8 +433,7 @@ def run_gpu_arm(args):
 
     peaks = load_measured_peaks()
     rays_per_launch = float(np.mean(kernel_rays))
-    spp_per_launch = SPP if bands else SPP // n_gpus
-    roofline = roofline_block(info0, n_pad, rays_per_launch, kms, expected_kernel(n_pad, spp_per_launch), peaks) if n_gpus == 1 else None
+    roofline = roofline_block(info0, n_pad, rays_per_launch, kms, step_kernel[0], peaks) if n_gpus == 1 else None
 
     # ---- HBM roofline of accumulate/tonemap standalone (A8-A9): resolve_sum_kernel -------------
     # 36 algorithmic bytes per pixel (16 R + 16 W accumulator, 4 W RGBA8); at N = 1 the
@@ -487,7 +478,7 @@ def run_gpu_arm(args):
                 m, rays2 = b.wait()
                 msl.append(m)
             entry = {"description": d2, "spheres": int(len(s2)), "mrays_per_s": rays2 / float(np.median(msl)) / 1e3, "kernel_ms": float(np.median(msl)),
-                     "rays": int(rays2), "kernel": expected_kernel((len(s2) + 7) // 8 * 8, spp2), "launches": reps}
+                     "rays": int(rays2), "kernel": b.last_kernel(), "launches": reps}
             g = gold.get(PARITY_KEYS.get(name, ""))
             if g is not None:
                 entry["parity_check"] = {"rgba_equal": sha(b.read_rgba8()) == g["rgba"], "accum_equal": sha(b.read_accum()) == g["accum"],

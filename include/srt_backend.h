@@ -213,6 +213,9 @@ void *srt_accum_device_ptr(srt_backend *b);
 void *srt_rgba_device_ptr(srt_backend *b);
 void *srt_cuda_stream(srt_backend *b);
 
+/* Introspection for benchmarks: the render kernel the last srt_render / srt_render_static launched, spelled as ncu and
+ * cuobjdump print it (e.g. "render_pool<8, 1, 896, 1, 0, 1>"); "" before the first render. */
+int srt_last_kernel(srt_backend *b, char *name, uint32_t capacity);
 /* Introspection for benchmarks: SM count, clock (kHz), kernel launches issued so far. */
 int srt_device_info(srt_backend *b, int *sm_count, int *clock_khz, uint64_t *launches);
 

@@ -39,7 +39,7 @@ EXPORTS = [
     "srt_filter_audit", "srt_write_accum", "srt_device_kat",
     "srt_comm_unique_id", "srt_comm_init_rank", "srt_comm_destroy", "srt_comm_info", "srt_set_partition",
     "srt_reduce_accum", "srt_gather_rgba", "srt_gather_accum", "srt_comm_group_begin", "srt_comm_group_end",
-    "srt_render_static",
+    "srt_render_static", "srt_last_kernel",
 ]
 STATIC_MAX_PIXELS = 2 << 20
 COMM_ID_BYTES = 128
@@ -102,6 +102,7 @@ def load_library():
         getattr(L, f).argtypes = [vp]
         getattr(L, f).restype = vp
     L.srt_device_info.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_uint64)]
+    L.srt_last_kernel.argtypes = [vp, C.c_char_p, C.c_uint32]
     L.srt_device_kat.argtypes = [vp, C.c_uint32, vp, C.c_uint32, vp]
     L.srt_comm_unique_id.argtypes = [vp]
     L.srt_comm_init_rank.argtypes = [vp, C.c_int, C.c_int, vp]
@@ -249,6 +250,12 @@ class Backend:
 
     def gather_accum(self, root=0):
         self._check(self.L.srt_gather_accum(self.h, root))
+
+    def last_kernel(self):
+        """The render kernel the last render launched, as ncu prints it."""
+        buf = C.create_string_buffer(128)
+        self._check(self.L.srt_last_kernel(self.h, buf, 128))
+        return buf.value.decode()
 
     def device_info(self):
         sm, khz, n = C.c_int(), C.c_int(), C.c_uint64()

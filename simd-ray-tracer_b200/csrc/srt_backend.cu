@@ -868,9 +868,9 @@ struct srt_backend {
     uint32_t fold_w_first = 0, fold_w_n = 0, fold_w_stride = 0;   // what d_fold_w currently holds
     std::vector<float2> h_fold_w;
     unsigned long long *h_rays = nullptr;   // pinned + mapped: written by the last CTA of a launch
-    std::vector<LaunchCfg> cfgs;
     bool in_flight = false;
     uint64_t launches = 0;
+    std::string last_kernel;             // the render kernel of the last srt_render / srt_render_static, as ncu prints it
     // multi-device (srt_comm_*): NCCL communicator of this handle, gather buffers on the root
     void *comm = nullptr;
     int comm_rank = 0, comm_size = 1;
@@ -1316,16 +1316,50 @@ static int make_params(srt_backend *b, const srt_camera *cam, const srt_render_a
     return SRT_OK;
 }
 
+// Name of a render kernel instantiation the way ncu / cuobjdump print it (bench.py matches its profile against it).
+static std::string kernel_label(const srt_scene_options &o, bool pool, bool stream, int pool_threads, bool bundle, bool packed) {
+    const int w = o.lane_width, fma = (w != 1 && o.fma_dot) ? 1 : 0;
+    char buf[96];
+    if (pool) snprintf(buf, sizeof(buf), "render_pool<%d, %d, %d, %d, %d, %d>", w, fma, pool_threads, stream ? kPoolMinBlocks : 1, stream ? 1 : 0, bundle ? 1 : 0);
+    else if (w == 1) snprintf(buf, sizeof(buf), "render_paths<1, 0, 0, 4, 4>");
+    else if (packed) snprintf(buf, sizeof(buf), "render_paths<%d, %d, 1, %d, %d>", w, fma, w == 4 ? 2 : 4, w == 4 ? 4 : 3);
+    else snprintf(buf, sizeof(buf), "render_paths<%d, %d, 0, 4, 4>", w, fma);
+    return buf;
+}
+
 // Attribute + occupancy calls of a (kernel, threads, shared memory) triple are made once per handle.
+// Function attributes belong to the (device, kernel) pair, not to a handle: several handles of one device share them, and
+// one handle renders scenes of different sizes with the same kernel.  The dynamic shared memory limit is therefore only
+// ever RAISED (a launch may use less than the limit, never more), the carve-out follows the launch that is about to run,
+// and all of it is cached process-wide per device so that the per-frame path makes no CUDA attribute call at all.
+struct KernelCfg {
+    int device; render_kernel_t kernel;
+    size_t smem_limit = 0;               // cudaFuncAttributeMaxDynamicSharedMemorySize currently set
+    int carve = -2;                      // cudaFuncAttributePreferredSharedMemoryCarveout currently set (-2: never)
+    std::vector<LaunchCfg> occ;          // occupancy per (threads, smem)
+};
+static std::mutex g_cfg_mu;
+static std::vector<KernelCfg> g_cfgs;
+
 static int launch_cfg(srt_backend *b, render_kernel_t kernel, int threads, size_t smem, int carve, int *per_sm) {
-    for (const LaunchCfg &c : b->cfgs)
-        if (c.kernel == kernel && c.threads == threads && c.smem == smem) { *per_sm = c.per_sm; return SRT_OK; }
-    SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (carve >= 0) SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+    std::lock_guard<std::mutex> lock(g_cfg_mu);
+    KernelCfg *k = nullptr;
+    for (KernelCfg &c : g_cfgs) if (c.device == b->device && c.kernel == kernel) { k = &c; break; }
+    if (!k) { g_cfgs.push_back(KernelCfg{b->device, kernel}); k = &g_cfgs.back(); }
+    if (smem > k->smem_limit) {
+        SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k->smem_limit = smem;
+    }
+    if (carve >= 0 && carve != k->carve) {
+        SRT_CUDA(b, cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
+        k->carve = carve;
+    }
+    for (const LaunchCfg &c : k->occ)
+        if (c.threads == threads && c.smem == smem) { *per_sm = c.per_sm; return SRT_OK; }
     int n = 0;
     SRT_CUDA(b, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem));
     if (n < 1) return fail(b, SRT_ERR_TOO_LARGE, "srt_render: kernel does not fit on an SM");
-    b->cfgs.push_back({kernel, threads, smem, n});
+    k->occ.push_back({kernel, threads, smem, n});
     *per_sm = n;
     return SRT_OK;
 }
@@ -1486,6 +1520,7 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     }
     if (stream) pool_threads = kPoolThreads;
     render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, use_bundle) : pick_kernel(b->opt, packed);
+    b->last_kernel = kernel_label(b->opt, pool, stream, pool_threads, use_bundle, packed);
     if (!kernel) return fail(b, SRT_ERR_INVALID, "srt_render: this build (SRT_FAST_BUILD) only carries the lane_width 8 + FMA kernels");
     const int threads = pool ? pool_threads : kBlockThreads;
     const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream, use_bundle) : (size_t)b->n_pad * sizeof(float4);
@@ -1586,6 +1621,7 @@ int srt_render_static(srt_backend *b, const srt_camera *cam, const srt_render_ar
     }
     if (stream) pool_threads = kPoolThreads;
     render_kernel_t kernel = pool ? pick_pool_kernel(b->opt, stream, pool_threads, false) : pick_kernel(b->opt, packed);
+    b->last_kernel = kernel_label(b->opt, pool, stream, pool_threads, false, packed);
     if (!kernel) return fail(b, SRT_ERR_INVALID, "srt_render_static: this build (SRT_FAST_BUILD) only carries the lane_width 8 + FMA kernels");
     const int threads = pool ? pool_threads : kBlockThreads;
     const size_t smem = pool ? pool_smem_bytes(b->n_pad, pool_threads, stream, false) : (size_t)b->n_pad * sizeof(float4);
@@ -1909,6 +1945,12 @@ static int gather_image(srt_backend *b, int root, bool accum, const char *who) {
 }
 int srt_gather_rgba(srt_backend *b, int root) { return b ? gather_image(b, root, false, "srt_gather_rgba") : SRT_ERR_INVALID; }
 int srt_gather_accum(srt_backend *b, int root) { return b ? gather_image(b, root, true, "srt_gather_accum") : SRT_ERR_INVALID; }
+
+int srt_last_kernel(srt_backend *b, char *name, uint32_t capacity) {
+    if (!b || !name || capacity == 0) return SRT_ERR_INVALID;
+    snprintf(name, capacity, "%s", b->last_kernel.c_str());
+    return SRT_OK;
+}
 
 int srt_device_info(srt_backend *b, int *sm_count, int *clock_khz, uint64_t *launches) {
     if (!b) return SRT_ERR_INVALID;

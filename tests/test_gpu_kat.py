@@ -67,3 +67,53 @@ def test_device_reflectance_and_normalize(backend, srt, kat):
     vin = np.array([v for v, _ in kat["normalize"]], np.uint32).view(np.float32)
     got = backend.device_kat(srt.KAT_NORMALIZE, vin)
     assert np.array_equal(got.view(np.uint32), np.array([o for _, o in kat["normalize"]], np.uint32))
+
+
+def test_last_kernel_names_the_launched_kernel(srt):
+    """srt_last_kernel: the instantiation srt_render picked, spelled as ncu prints it (bench.py matches its ncu profile
+    against this name instead of guessing)."""
+    b = srt.Backend(0)
+    try:
+        assert b.last_kernel() == ""
+        cases = [(3, 8, True, 64, 36, 16, "render_pool<8, 1, 896, 1, 0, 1>"),      # 1,024 spheres, >= 8 samples: bundle mode
+                 (3, 8, True, 64, 36, 2, "render_pool<8, 1, 896, 1, 0, 0>"),
+                 (3, 1, False, 64, 36, 2, "render_pool<1, 0, 896, 1, 0, 0>"),       # RenderTileScalar semantics
+                 (0, 8, True, 64, 36, 2, "render_paths<8, 1, 0, 4, 4>"),            # 5 spheres: one path per thread
+                 (1, 4, False, 64, 36, 2, "render_pool<4, 0, 896, 1, 0, 0>"),       # 256 spheres, SSE profile
+                 (4, 8, True, 32, 18, 8, "render_pool<8, 1, 256, 2, 1, 1>")]        # 65,536 spheres: streamed tables
+        for scene, lanes, fma, w, h, spp, want in cases:
+            sp, sky, hdr = srt.host_scene(scene)
+            b.set_scene(sp, sky, lanes, fma)
+            b.resize(w, h)
+            b.render(srt.host_camera(scene, w, h, hdr), 0, spp)
+            b.wait()
+            assert b.last_kernel() == want, (scene, lanes, fma, spp)
+        b.render_static(srt.host_camera(4, 32, 18, hdr), 8, 8)                       # no bundle mode without allocations
+        b.wait()
+        assert b.last_kernel() == "render_pool<8, 1, 256, 2, 1, 0>"
+    finally:
+        b.close()
+
+
+def test_one_kernel_scenes_of_different_sizes_in_any_order(srt, oracle):
+    """The dynamic shared memory limit of a kernel is a per-device function attribute shared by every handle and every
+    scene size: it may only be raised.  Small -> large -> medium -> large on one kernel instantiation (and a second
+    handle rendering a small scene in between) used to leave the limit at the medium size: `invalid argument` at the next
+    launch of the large scene."""
+    spheres, sky, hdr = oracle.scene(2)
+    w, h = 48, 27
+    cam = oracle.camera(hdr, w, h)
+    a, b = srt.Backend(0), srt.Backend(0)
+    try:
+        for n, handle in ((104, a), (482, a), (296, a), (482, a), (80, b), (482, a), (482, b)):
+            sub = spheres[:n].copy()
+            handle.set_scene(sub, sky, 4, False)
+            handle.resize(w, h)
+            handle.render(cam, 0, 2)
+            _, rays = handle.wait()
+            assert handle.last_kernel() == "render_pool<4, 0, 896, 1, 0, 0>"
+            o = oracle.render(sub, sky, 4, 0, cam, w, h, 0, 2)
+            assert rays == o["rays"] and np.array_equal(handle.read_accum().view(np.uint32), o["accum"].view(np.uint32)), n
+    finally:
+        a.close()
+        b.close()
