@@ -335,6 +335,8 @@ def load_host_library():
         H.srt_host_scene_hash.restype = C.c_ulonglong
         H.srt_host_save_checkpoint.argtypes = [C.c_char_p, C.c_void_p, C.c_ulonglong, C.c_void_p]
         H.srt_host_load_checkpoint.argtypes = [C.c_char_p, C.c_void_p, C.POINTER(C.c_ulonglong), C.c_void_p, C.c_ulonglong]
+        H.srt_host_write_image.argtypes = [C.c_char_p, C.c_void_p, C.c_uint, C.c_uint, C.c_int]
+        H.srt_host_write_pfm.argtypes = [C.c_char_p, C.c_void_p, C.c_uint, C.c_uint]
         _hostlib = H
     return _hostlib
 
@@ -354,6 +356,20 @@ def load_scene_file(index, path):
 def reset_scene(index):
     """Undo load_scene_file: slot `index` is rebuilt as the built-in / synthetic scene on next use."""
     load_host_library().srt_host_reset_scene(index)
+
+
+def write_image(path, rgba, kind=0):
+    """Write a presented image (H x W uint32 RGBA8, row 0 = bottom) as PPM or PNG (kind 0: by extension, 1 PPM, 2 PNG)."""
+    a = np.ascontiguousarray(rgba, np.uint32)
+    if a.ndim != 2 or load_host_library().srt_host_write_image(os.fsencode(path), a.ctypes.data, a.shape[1], a.shape[0], int(kind)) != 0:
+        raise SrtError(f"cannot write image {path}")
+
+
+def write_pfm(path, accum):
+    """Write a linear accumulator (H x W x 4 float32) as an RGB PFM image."""
+    a = np.ascontiguousarray(accum, np.float32)
+    if a.ndim != 3 or a.shape[2] != 4 or load_host_library().srt_host_write_pfm(os.fsencode(path), a.ctypes.data, a.shape[1], a.shape[0]) != 0:
+        raise SrtError(f"cannot write image {path}")
 
 
 def host_scene_hash(index):

@@ -95,6 +95,11 @@ u32 GetSceneGeneration(u32 SceneIndex);                 // bumped by SetScene / 
 bool SaveCheckpoint(const char *Path, const checkpoint_header &Header, const f32 *Accum);
 bool LoadCheckpoint(const char *Path, checkpoint_header *Header, std::vector<f32> *Accum);
 bool SaveSceneFile(const char *Path, const scene &Scene);
+// Presented image (RGBA8, row 0 = image bottom) and linear accumulator to files; rows are flipped to top-down on the way out.
+bool WritePpm(const char *Path, const u32 *Pixels, u32 W, u32 H);
+bool WritePng(const char *Path, const u32 *Pixels, u32 W, u32 H);
+bool WriteImage(const char *Path, const u32 *Pixels, u32 W, u32 H);   // by extension: .png -> PNG, anything else PPM
+bool WritePfm(const char *Path, const f32 *Accum, u32 W, u32 H);
 bool LoadSceneFile(const char *Path, scene *Out);       // allocates Out->ScalarSpheres
 // Replace scene slot `SceneIndex` (0..SceneCount-1) by a loaded scene; the next OnRender with
 // that index uploads it.  Resume: continue an accumulation from a checkpoint (the next

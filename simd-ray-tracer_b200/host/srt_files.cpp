@@ -106,3 +106,114 @@ bool LoadSceneFile(const char *Path, scene *Out) {
     Out->Name = "scene file";
     return true;
 }
+
+// ---- images ----------------------------------------------------------------------------------------
+// The reference presents `image` through a GL texture / an HTML canvas (win32.cpp, wasm.cpp:176-219); the
+// headless driver writes it to a file instead.  Row 0 of the reference's image is the BOTTOM row (GL
+// convention), so every writer below emits rows in reverse order.
+
+bool WritePpm(const char *Path, const u32 *Pixels, u32 W, u32 H) {
+    FILE *F = fopen(Path, "wb");
+    if (!F) return false;
+    fprintf(F, "P6\n%u %u\n255\n", W, H);
+    std::vector<u8> Row((size_t)W * 3);
+    bool Ok = true;
+    for (u32 y = 0; y < H && Ok; ++y) {
+        const u32 *Src = Pixels + (size_t)(H - 1 - y) * W;
+        for (u32 x = 0; x < W; ++x) { Row[x * 3 + 0] = Src[x] & 0xFF; Row[x * 3 + 1] = (Src[x] >> 8) & 0xFF; Row[x * 3 + 2] = (Src[x] >> 16) & 0xFF; }
+        Ok = fwrite(Row.data(), 1, Row.size(), F) == Row.size();
+    }
+    return (fclose(F) == 0) && Ok;
+}
+
+// PFM (portable float map): RGB f32, little endian, rows bottom-up -- the accumulator's own row order.
+bool WritePfm(const char *Path, const f32 *Accum, u32 W, u32 H) {
+    FILE *F = fopen(Path, "wb");
+    if (!F) return false;
+    fprintf(F, "PF\n%u %u\n-1.0\n", W, H);
+    std::vector<f32> Row((size_t)W * 3);
+    bool Ok = true;
+    for (u32 y = 0; y < H && Ok; ++y) {
+        const f32 *Src = Accum + (size_t)y * W * 4;
+        for (u32 x = 0; x < W; ++x) { Row[x * 3 + 0] = Src[x * 4 + 0]; Row[x * 3 + 1] = Src[x * 4 + 1]; Row[x * 3 + 2] = Src[x * 4 + 2]; }
+        Ok = fwrite(Row.data(), sizeof(f32), Row.size(), F) == Row.size();
+    }
+    return (fclose(F) == 0) && Ok;
+}
+
+// PNG, 8-bit RGB, filter 0 on every row, zlib stream of STORED deflate blocks (no compressor in this tree and no
+// zlib dependency: the file is 0.02 % larger than the PPM and every PNG reader opens it).
+namespace {
+struct Crc32 {
+    u32 Table[256];
+    Crc32() {
+        for (u32 n = 0; n < 256; ++n) {
+            u32 c = n;
+            for (int k = 0; k < 8; ++k) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+            Table[n] = c;
+        }
+    }
+    u32 Update(u32 Crc, const u8 *P, size_t N) const {
+        for (size_t i = 0; i < N; ++i) Crc = Table[(Crc ^ P[i]) & 0xFF] ^ (Crc >> 8);
+        return Crc;
+    }
+};
+void PutBe32(std::vector<u8> &V, u32 X) { V.push_back((u8)(X >> 24)); V.push_back((u8)(X >> 16)); V.push_back((u8)(X >> 8)); V.push_back((u8)X); }
+bool WriteChunk(FILE *F, const Crc32 &Crc, const char Type[4], const std::vector<u8> &Data) {
+    std::vector<u8> Head, Tail;
+    PutBe32(Head, (u32)Data.size());
+    Head.insert(Head.end(), Type, Type + 4);
+    u32 C = Crc.Update(0xFFFFFFFFu, Head.data() + 4, 4);
+    C = Crc.Update(C, Data.data(), Data.size()) ^ 0xFFFFFFFFu;
+    PutBe32(Tail, C);
+    return fwrite(Head.data(), 1, 8, F) == 8 && (Data.empty() || fwrite(Data.data(), 1, Data.size(), F) == Data.size()) &&
+           fwrite(Tail.data(), 1, 4, F) == 4;
+}
+} // namespace
+
+bool WritePng(const char *Path, const u32 *Pixels, u32 W, u32 H) {
+    if (!W || !H) return false;
+    static const Crc32 Crc;
+    const size_t Stride = (size_t)W * 3 + 1, RawSize = Stride * H;
+    if (RawSize / 65535u * 5u + RawSize + 64u > 0x7FFFFFFFull) return false;      // one IDAT chunk: length field is 31 bits
+    std::vector<u8> Raw(RawSize);
+    for (u32 y = 0; y < H; ++y) {
+        const u32 *Src = Pixels + (size_t)(H - 1 - y) * W;
+        u8 *Dst = Raw.data() + Stride * y;
+        *Dst++ = 0;                                                              // filter type None
+        for (u32 x = 0; x < W; ++x) { *Dst++ = Src[x] & 0xFF; *Dst++ = (Src[x] >> 8) & 0xFF; *Dst++ = (Src[x] >> 16) & 0xFF; }
+    }
+    std::vector<u8> Z;
+    Z.reserve(RawSize + RawSize / 65535u * 5u + 16u);
+    Z.push_back(0x78); Z.push_back(0x01);                                        // zlib header: deflate, 32K window, no preset dictionary
+    u32 A = 1, B = 0;                                                            // Adler-32 of the raw bytes
+    for (size_t At = 0; At < RawSize;) {
+        const size_t N = RawSize - At < 65535u ? RawSize - At : 65535u;
+        Z.push_back(At + N == RawSize ? 1 : 0);                                  // BFINAL, BTYPE = 00 (stored)
+        Z.push_back((u8)N); Z.push_back((u8)(N >> 8)); Z.push_back((u8)~N); Z.push_back((u8)(~N >> 8));
+        Z.insert(Z.end(), Raw.begin() + At, Raw.begin() + At + N);
+        for (size_t i = 0; i < N;) {                                             // 5552 bytes keep B below 2^32 between reductions
+            const size_t M = N - i < 5552u ? N - i : 5552u;
+            for (size_t k = 0; k < M; ++k) { A += Raw[At + i + k]; B += A; }
+            A %= 65521u; B %= 65521u;
+            i += M;
+        }
+        At += N;
+    }
+    PutBe32(Z, (B << 16) | A);
+    FILE *F = fopen(Path, "wb");
+    if (!F) return false;
+    static const u8 Sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
+    std::vector<u8> Ihdr;
+    PutBe32(Ihdr, W); PutBe32(Ihdr, H);
+    Ihdr.push_back(8); Ihdr.push_back(2); Ihdr.push_back(0); Ihdr.push_back(0); Ihdr.push_back(0);   // 8 bit, truecolour, deflate, adaptive, no interlace
+    const bool Ok = fwrite(Sig, 1, 8, F) == 8 && WriteChunk(F, Crc, "IHDR", Ihdr) && WriteChunk(F, Crc, "IDAT", Z) &&
+                    WriteChunk(F, Crc, "IEND", std::vector<u8>());
+    return (fclose(F) == 0) && Ok;
+}
+
+bool WriteImage(const char *Path, const u32 *Pixels, u32 W, u32 H) {
+    const size_t L = strlen(Path);
+    const bool Png = L >= 4 && (strcmp(Path + L - 4, ".png") == 0 || strcmp(Path + L - 4, ".PNG") == 0);
+    return Png ? WritePng(Path, Pixels, W, H) : WritePpm(Path, Pixels, W, H);
+}

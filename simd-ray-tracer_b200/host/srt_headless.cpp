@@ -13,39 +13,11 @@
 #include <string>
 #include <vector>
 
-static bool WritePpm(const char *Path, const u32 *Pixels, u32 W, u32 H) {
-    FILE *F = fopen(Path, "wb");
-    if (!F) return false;
-    fprintf(F, "P6\n%u %u\n255\n", W, H);
-    std::vector<u8> Row(W * 3);
-    for (u32 y = 0; y < H; ++y) {
-        const u32 *Src = Pixels + (size_t)(H - 1 - y) * W;
-        for (u32 x = 0; x < W; ++x) { Row[x * 3 + 0] = Src[x] & 0xFF; Row[x * 3 + 1] = (Src[x] >> 8) & 0xFF; Row[x * 3 + 2] = (Src[x] >> 16) & 0xFF; }
-        fwrite(Row.data(), 1, Row.size(), F);
-    }
-    fclose(F);
-    return true;
-}
-
-// PFM (portable float map): RGB f32, little endian, rows bottom-up -- the accumulator's own row order.
-static bool WritePfm(const char *Path, const f32 *Accum, u32 W, u32 H) {
-    FILE *F = fopen(Path, "wb");
-    if (!F) return false;
-    fprintf(F, "PF\n%u %u\n-1.0\n", W, H);
-    std::vector<f32> Row((size_t)W * 3);
-    for (u32 y = 0; y < H; ++y) {
-        const f32 *Src = Accum + (size_t)y * W * 4;
-        for (u32 x = 0; x < W; ++x) { Row[x * 3 + 0] = Src[x * 4 + 0]; Row[x * 3 + 1] = Src[x * 4 + 1]; Row[x * 3 + 2] = Src[x * 4 + 2]; }
-        fwrite(Row.data(), sizeof(f32), Row.size(), F);
-    }
-    return fclose(F) == 0;
-}
-
 static void Usage() {
     fprintf(stderr,
             "usage: srt_headless [--scene 0..4] [--width W] [--height H] [--spp N] [--spf K]\n"
             "                    [--simd 0|1] [--lanes 4|8] [--fma 0|1] [--device D] [--gpus N] [--stream-base B]\n"
-            "                    [--orbit FRAMES] [--out image.ppm] [--accum accum.f32]\n"
+            "                    [--orbit FRAMES] [--out image.ppm|image.png] [--accum accum.f32]\n"
             "                    [--scene-file in.scene] [--dump-scene out.scene]\n"
             "                    [--checkpoint out.ckpt] [--resume in.ckpt] [--pfm accum.pfm] [--threads N]\n"
             "  scenes: 0 RGB Glass, 1 Floating Spheres, 2 One Weekend, 3 synthetic 1,024, 4 synthetic 65,536\n"
@@ -158,7 +130,7 @@ int main(int argc, char **argv) {
     FrameMs.push_back(LastMs); TotalRays += LastRays; TotalMs += LastMs;
     const f64 Wall = QueryTimestampInMilliseconds() - Wall0;
 
-    if (Out && !WritePpm(Out, Present.data(), W, H)) { fprintf(stderr, "cannot write %s\n", Out); return 1; }
+    if (Out && !WriteImage(Out, Present.data(), W, H)) { fprintf(stderr, "cannot write %s\n", Out); return 1; }
     if (CkptOut) {
         std::vector<f32> Acc((size_t)W * H * 4);
         ReadAccumulator(Acc.data());

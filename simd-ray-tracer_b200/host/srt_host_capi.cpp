@@ -67,4 +67,11 @@ int srt_host_load_checkpoint(const char *path, unsigned *header, unsigned long l
     return 0;
 }
 
+// Image writers of the headless driver (srt_files.cpp).  kind: 0 = by extension, 1 = PPM, 2 = PNG.
+int srt_host_write_image(const char *path, const unsigned *rgba, unsigned w, unsigned h, int kind) {
+    const bool Ok = kind == 1 ? WritePpm(path, rgba, w, h) : (kind == 2 ? WritePng(path, rgba, w, h) : WriteImage(path, rgba, w, h));
+    return Ok ? 0 : -1;
+}
+int srt_host_write_pfm(const char *path, const float *accum, unsigned w, unsigned h) { return WritePfm(path, accum, w, h) ? 0 : -1; }
+
 }

@@ -151,3 +151,50 @@ def test_magic_division_is_exact():
         # (x * m) < 2^62 fits uint64
         q = (xs * np.uint64(m)) >> np.uint64(30 + l)
         assert np.array_equal(q, xs // np.uint64(d)), d
+
+
+def _read_png(path):
+    """Minimal independent PNG reader (8-bit RGB, filter 0 only): checks signature, chunk CRCs, zlib stream."""
+    import struct
+    import zlib
+    data = open(path, "rb").read()
+    assert data[:8] == b"\x89PNG\r\n\x1a\n"
+    at, chunks = 8, []
+    while at < len(data):
+        (n,) = struct.unpack(">I", data[at:at + 4])
+        typ, body = data[at + 4:at + 8], data[at + 8:at + 8 + n]
+        (crc,) = struct.unpack(">I", data[at + 8 + n:at + 12 + n])
+        assert zlib.crc32(typ + body) == crc, typ
+        chunks.append((typ, body))
+        at += 12 + n
+    assert [c[0] for c in chunks] == [b"IHDR", b"IDAT", b"IEND"]
+    w, h, depth, colour, comp, flt, lace = struct.unpack(">IIBBBBB", chunks[0][1])
+    assert (depth, colour, comp, flt, lace) == (8, 2, 0, 0, 0)
+    raw = np.frombuffer(zlib.decompress(chunks[1][1]), np.uint8).reshape(h, 1 + 3 * w)   # checks Adler-32 too
+    assert not raw[:, 0].any()
+    return raw[:, 1:].reshape(h, w, 3)
+
+
+@pytest.mark.parametrize("w,h", [(1, 1), (7, 5), (300, 90), (257, 256)])   # 300x90 and 257x256 span several 65,535-byte stored blocks
+def test_image_writers(srt, tmp_path, w, h):
+    rng = np.random.default_rng(w * 1000 + h)
+    rgba = rng.integers(0, 2**32, size=(h, w), dtype=np.uint32)
+    want = np.stack([(rgba >> s) & 0xFF for s in (0, 8, 16)], axis=-1).astype(np.uint8)[::-1]   # file rows are top-down
+    png, ppm = tmp_path / "a.png", tmp_path / "a.ppm"
+    srt.write_image(png, rgba)
+    srt.write_image(ppm, rgba)
+    assert np.array_equal(_read_png(png), want)
+    blob = open(ppm, "rb").read()
+    head = b"P6\n%d %d\n255\n" % (w, h)
+    assert blob.startswith(head) and len(blob) == len(head) + 3 * w * h
+    assert np.array_equal(np.frombuffer(blob[len(head):], np.uint8).reshape(h, w, 3), want)
+    srt.write_image(tmp_path / "b.ppm", rgba, kind=2)                      # explicit kind beats the extension
+    assert np.array_equal(_read_png(tmp_path / "b.ppm"), want)
+    acc = rng.standard_normal((h, w, 4)).astype(np.float32)
+    srt.write_pfm(tmp_path / "a.pfm", acc)
+    blob = open(tmp_path / "a.pfm", "rb").read()
+    head = b"PF\n%d %d\n-1.0\n" % (w, h)
+    assert blob.startswith(head)
+    assert np.array_equal(np.frombuffer(blob[len(head):], np.float32).reshape(h, w, 3), acc[:, :, :3])
+    with pytest.raises(srt.SrtError):
+        srt.write_image(tmp_path / "no_such_dir" / "a.png", rgba)
