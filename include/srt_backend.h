@@ -84,7 +84,9 @@ typedef struct srt_render_args {
     uint32_t sample_stride;  /* k advances by this; 1 = contiguous; G for sample sharding over G devices */
     uint32_t accum_mode;     /* srt_accum_mode */
     uint64_t stream_base;    /* per-path RNG stream = scramble(stream_base + k*W*H + y*W + x),
-                                scramble = main.cpp:667-676 on a 64-bit index */
+                                scramble = main.cpp:667-676 on a 64-bit index, a zero shift count
+                                (i % 64 == 57 / 41: the reference's expression zeroes the seed there)
+                                replaced by 32 -- DESIGN.md section 3 */
     uint32_t record_primary; /* 1: record primary-ray hit/primitive/t of sample `first_sample` */
     uint32_t _reserved;
 } srt_render_args;

@@ -32,13 +32,16 @@ static uint32_t *SrtRefTapPrim = 0;            // debug tap: primary-ray primiti
 static float *SrtRefTapT = 0;                  // debug tap: primary-ray MinT
 static uint32_t SrtRefTapSample = 0;           // which sample index the taps record
 
-// Per-stream seed: main.cpp:667-676 evaluated on a 64-bit index.
+// Per-stream seed: main.cpp:667-676 evaluated on a 64-bit index.  A shift count of zero
+// (i % 64 == 57 / == 41: `S ^= S >> 0` zeroes the seed, so all those indices would share ONE stream) is
+// replaced by 32; every other index gets the reference's value (checked against srt_ref_thread_seed).
 static inline uint64_t SrtRefStreamSeed(uint64_t i) {
     uint64_t S = 0x420247153476526ULL * i;
     S += 0x8442885C91A5C8DULL;
-    S ^= S >> ((7 + i) % 64);
+    const unsigned K1 = (unsigned)((7 + i) % 64), K2 = (unsigned)((0x29 ^ i) % 64);
+    S ^= S >> (K1 ? K1 : 32);
     S ^= S << 23;
-    S ^= S >> ((0x29 ^ i) % 64);
+    S ^= S >> (K2 ? K2 : 32);
     S = (S * 0x11C19226CEB4769AULL) + 0x1105404122082911ULL;
     S ^= S << 19;
     S ^= S >> 13;
@@ -223,6 +226,7 @@ f64 WorkQueueGetCompletionTime() { return SrtRefCompletionTime; }
 // C entry points (ctypes-friendly).  All of them are test/baseline plumbing.
 // ===================================================================================
 extern "C" {
+uint64_t srt_ref_thread_seed(uint32_t i);
 
 static bool SrtRefInitDone = false;
 static void *SrtRefPresentBuffer = 0;   // the platform-owned `image` OnRender copies into
@@ -285,7 +289,7 @@ int srt_ref_render(int scene, uint32_t w, uint32_t h, uint32_t spp, int enable_s
     // The as-shipped RNG is per worker thread and sequential; re-seed exactly as OnInit
     // does (main.cpp:667-678) so that every call is reproducible at 1 thread.
     for (u32 i = 0; i < SrtRefMaxThreads; ++i) {
-        ThreadContexts[i].RandomState.Seed = SrtRefStreamSeed(i);
+        ThreadContexts[i].RandomState.Seed = srt_ref_thread_seed(i);   // the reference's own expression, zero shifts included
         ThreadContexts[i].RaysCastInThread = 0;
     }
 
@@ -355,6 +359,7 @@ void srt_ref_rng(uint64_t seed, uint32_t n, float mn, float mx, int as_float, vo
         else ((uint32_t *)out)[i] = S.PCG();                       // base.h:954-963
     }
 }
+uint64_t srt_ref_stream_seed(uint64_t i) { return SrtRefStreamSeed(i); }   // the P10 stream contract
 uint64_t srt_ref_thread_seed(uint32_t i) {   // main.cpp:667-676 with the reference's u32 index
     u64 InitialSeed = 0x420247153476526ULL * (u64)i;
     InitialSeed += 0x8442885C91A5C8DULL;

@@ -63,13 +63,16 @@ float orc_random_float(uint64_t *state, float mn, float mx) {
     float r = (float)n * inv;
     return r + mn;
 }
-/* ---- A10: main.cpp:667-676, index widened to 64 bits ------------------------------- */
+/* ---- A10: main.cpp:667-676, index widened to 64 bits; a shift count of 0 (i % 64 == 57 / == 41, where the
+ * reference's `s ^= s >> 0` zeroes the seed and every such index would share one stream) is replaced by 32:
+ * the stream contract of DESIGN.md section 3.  Equal to the reference for every other index. ------------- */
 uint64_t orc_stream_seed(uint64_t i) {
     uint64_t s = 0x420247153476526ULL * i;
     s += 0x8442885C91A5C8DULL;
-    s ^= s >> ((7 + i) % 64);
+    unsigned k1 = (unsigned)((7 + i) % 64), k2 = (unsigned)((0x29 ^ i) % 64);
+    s ^= s >> (k1 ? k1 : 32);
     s ^= s << 23;
-    s ^= s >> ((0x29 ^ i) % 64);
+    s ^= s >> (k2 ? k2 : 32);
     s = (s * 0x11C19226CEB4769AULL) + 0x1105404122082911ULL;
     s ^= s << 19;
     s ^= s >> 13;

@@ -28,7 +28,7 @@ typedef struct { float position[4], z[4], x[4], y[4], film_center[4]; float film
 /* A7  base.h:954-963, 983-989 */
 uint32_t orc_pcg(uint64_t *state);
 float orc_random_float(uint64_t *state, float mn, float mx);
-/* A10 main.cpp:667-676 on a 64-bit index */
+/* A10 main.cpp:667-676 on a 64-bit index; a zero shift count (i % 64 == 57 / 41) replaced by 32 */
 uint64_t orc_stream_seed(uint64_t index);
 /* A2  x64_math.h:234-245 (IEEE; NormalizeFast == Normalize per wasm_math.h:168-170) */
 void orc_normalize(const float in[3], float out[3]);

@@ -78,13 +78,18 @@ __device__ __forceinline__ uint32_t pcg_next(uint64_t &s) {
 __device__ __forceinline__ float rand_float(uint64_t &s, float inv_range, float mn) {
     return __fadd_rn(__fmul_rn(__uint2float_rn(pcg_next(s)), inv_range), mn);
 }
-// Per-path stream seed: main.cpp:667-676 evaluated on a 64-bit index.
+// Per-path stream seed: main.cpp:667-676 evaluated on a 64-bit index, with ONE change: a shift count of zero
+// becomes 32.  In the reference's expression `s ^= s >> 0` zeroes the seed, so every index with i % 64 == 57
+// (first shift) or == 41 (second shift) ends on the SAME value.  The reference only ever feeds it thread numbers;
+// fed path indices, 1/32 of all paths -- whole pixel columns when W*H % 64 == 0 -- would share one stream for
+// every sample and never converge (stream contract).  All other indices keep the reference's value.
 __host__ __device__ __forceinline__ uint64_t stream_seed(uint64_t i) {
     uint64_t s = 0x420247153476526ULL * i;
     s += 0x8442885C91A5C8DULL;
-    s ^= s >> ((7 + i) % 64);
+    const uint32_t k1 = (uint32_t)(7 + i) & 63u, k2 = (uint32_t)(0x29 ^ i) & 63u;
+    s ^= s >> (k1 ? k1 : 32u);
     s ^= s << 23;
-    s ^= s >> ((0x29 ^ i) % 64);
+    s ^= s >> (k2 ? k2 : 32u);
     s = (s * 0x11C19226CEB4769AULL) + 0x1105404122082911ULL;
     s ^= s << 19;
     s ^= s >> 13;

@@ -43,6 +43,15 @@ def main():
     kat = {}
     seeds = [R.L.srt_ref_thread_seed(i) for i in range(4)] + [0x29D7A0A514F22432, 0xCD46749A57ACB371]
     kat["thread_seeds"] = [int(x) for x in seeds[:4]]
+    # the stream contract (oracle/ref_platform.cpp SrtRefStreamSeed): indices around the reference's zero-shift cases
+    # (i % 64 == 41, 57), a 64-bit index, and a plain run; equal to the thread seed wherever that one is not degenerate
+    idx = list(range(4)) + [41, 57, 105, 121, 64 * 32400 + 57, (1 << 40) + 41, (1 << 63) - 7, 1000, 123456789]
+    kat["stream_seed_index"] = [int(i) for i in idx]
+    kat["stream_seeds"] = [int(R.L.srt_ref_stream_seed(i)) for i in idx]
+    for i in range(64):
+        if i not in (41, 57):
+            assert R.L.srt_ref_stream_seed(i) == R.L.srt_ref_thread_seed(i)
+    assert len({R.L.srt_ref_stream_seed(i) for i in range(1 << 16)}) == 1 << 16
     rng = {}
     for sd in seeds:
         u = np.zeros(16, np.uint32)

@@ -131,6 +131,8 @@ class Ref:
         L.srt_ref_rng.argtypes = [C.c_uint64, C.c_uint32, C.c_float, C.c_float, C.c_int, C.c_void_p]
         L.srt_ref_thread_seed.restype = C.c_uint64
         L.srt_ref_thread_seed.argtypes = [C.c_uint32]
+        L.srt_ref_stream_seed.restype = C.c_uint64
+        L.srt_ref_stream_seed.argtypes = [C.c_uint64]
         L.srt_ref_linear_to_srgb.restype = C.c_float
         L.srt_ref_linear_to_srgb.argtypes = [C.c_float]
         L.srt_ref_pack.restype = C.c_uint32

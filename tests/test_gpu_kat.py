@@ -37,6 +37,11 @@ def test_device_pcg_and_random_float(backend, srt, kat):
 def test_device_stream_seed(backend, srt, kat):
     got = backend.device_kat(srt.KAT_STREAM_SEED, np.arange(4, dtype=np.uint64))
     assert [int(x) for x in got[:, 0]] == kat["thread_seeds"]
+    # the stream contract around the reference's zero-shift indices (i % 64 == 41, 57) and on 64-bit indices
+    got = backend.device_kat(srt.KAT_STREAM_SEED, np.array(kat["stream_seed_index"], dtype=np.uint64))
+    assert [int(x) for x in got[:, 0]] == kat["stream_seeds"]
+    got = backend.device_kat(srt.KAT_STREAM_SEED, np.arange(1 << 14, dtype=np.uint64))
+    assert len(set(int(x) for x in got[:, 0])) == 1 << 14
 
 
 def test_device_tonemap_and_pack_edge_values(backend, srt, kat):

@@ -57,6 +57,9 @@ def test_images(oracle, gold, scene, mode):
 def test_rng_kat(oracle, kat):
     L = oracle.L
     assert [L.orc_stream_seed(i) for i in range(4)] == kat["thread_seeds"]
+    # stream contract: the reference's expression except where it zeroes the seed (i % 64 == 41, 57)
+    assert [L.orc_stream_seed(i) for i in kat["stream_seed_index"]] == kat["stream_seeds"]
+    assert len({L.orc_stream_seed(i) for i in range(1 << 14)}) == 1 << 14          # no two indices share a stream
     for seed, e in kat["rng"].items():
         st = C.c_uint64(int(seed))
         assert [L.orc_pcg(C.byref(st)) for _ in range(16)] == e["pcg"]
