@@ -22,7 +22,7 @@ sys.path.insert(0, os.path.dirname(HERE))
 import orclib  # noqa: E402
 
 W, H, SPP = 128, 72, 512
-CASES = [(0, "w8", 1), (2, "w8", 1)]     # (scene, lib, EnableSIMD)
+CASES = [(0, "w8", 1), (2, "w8", 1), (1, "w4", 0)]     # (scene, lib, EnableSIMD): AVX2 RenderTile twice, RenderTileScalar once
 
 
 def main():

@@ -18,8 +18,8 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_asshipped_stats.npz")
 
 
-def _render(backend, sp, sky, cam, w, h, spp, base):
-    backend.set_scene(sp, sky, 8, True)
+def _render(backend, sp, sky, mode, cam, w, h, spp, base):
+    backend.set_scene(sp, sky, mode[0], bool(mode[1]))
     if (backend.width, backend.height) != (w, h):
         backend.resize(w, h)
     backend.reset()
@@ -32,8 +32,8 @@ def _rms(a):
     return float(np.sqrt(np.mean(np.square(a))))
 
 
-@pytest.mark.parametrize("scene", [0, 2])
-def test_contract_render_differs_from_the_shipped_reference_by_noise_only(backend, oracle, scene):
+@pytest.mark.parametrize("scene,mode", [(0, (8, 1)), (2, (8, 1)), (1, (1, 0))])   # the profiles the goldens were rendered in
+def test_contract_render_differs_from_the_shipped_reference_by_noise_only(backend, oracle, scene, mode):
     gold = np.load(GOLD)
     w, h, spp = (int(x) for x in gold["size"])
     sp, sky, hdr = oracle.scene(scene)
@@ -42,8 +42,8 @@ def test_contract_render_differs_from_the_shipped_reference_by_noise_only(backen
     for off, n in ((0, 3), (4, 3), (8, 3), (12, 3), (16, 3), (20, 2)):        # v3 fields are padded to 4 floats
         assert mine[off:off + n].tobytes() == ref_cam[off:off + n].tobytes()
     ref = np.clip(gold[f"s{scene}_accum"].astype(np.float64), 0.0, 2.0)
-    a = _render(backend, sp, sky, cam, w, h, spp, 0)
-    b = _render(backend, sp, sky, cam, w, h, spp, 1 << 40)
+    a = _render(backend, sp, sky, mode, cam, w, h, spp, 0)
+    b = _render(backend, sp, sky, mode, cam, w, h, spp, 1 << 40)
     d_ref, d_self = a - ref, a - b
     # same noise level overall, no offset
     assert 0.85 < _rms(d_ref) / _rms(d_self) < 1.15
