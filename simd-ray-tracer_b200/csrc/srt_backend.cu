@@ -250,6 +250,18 @@ __device__ __forceinline__ void fold_chunk(const KernelParams &P, uint32_t pix, 
     *(volatile uint32_t *)&P.done[pix] = P.done_tag | (c + 1u);
 }
 
+#ifdef SRT_SPIN_LIMIT
+// Debug build: who holds each path slot (0 = in a ring, 1 + warp = held by that warp, 0xFFFF = retired).  A slot id taken
+// twice (site 30) or pushed / retired by a warp that does not hold it (sites 31-33) is a broken ring protocol; sites 16-26, 34
+// check the indices read from slot state and queues before they are used.  The report (site, CTA, thread, one value) comes
+// back through srt_wait.  History: the first run of scripts/soak.py on this build found the missing __syncwarp() after the
+// ring pops.
+__device__ unsigned int g_dbg_owner[1024 * 2048];
+#define SRT_OWN_SET(site, s, expect, val) do { const unsigned int o_ = atomicExch(&g_dbg_owner[(blockIdx.x & 1023u) * 2048u + (s)], (val)); \
+        SRT_CHECKV(site, o_ == (expect), ((unsigned long long)o_ << 32) | ((s) << 8) | kind); } while (0)
+#else
+#define SRT_OWN_SET(site, s, expect, val) do { } while (0)
+#endif
 template <int W, bool FMA, int THREADS, int MINB, bool STREAM, bool BUNDLE = false>
 __global__ void __launch_bounds__(THREADS, MINB)
 render_pool(const __grid_constant__ KernelParams P) {
@@ -298,6 +310,11 @@ render_pool(const __grid_constant__ KernelParams P) {
             SRT_SU(S_KEND, i) = k_end;
             SRT_SU(S_FLAGS, i) = 0u;
         }
+#ifdef SRT_SPIN_LIMIT
+        SRT_CHECK(15, gridDim.x <= kDbgCtas);
+        for (uint32_t i = tid; i < 2048u; i += THREADS) g_dbg_owner[(blockIdx.x & 1023u) * 2048u + i] = 0u;
+        for (uint32_t i = tid; i < 3u * 2048u; i += THREADS) { g_dbg_busy[dbg_ring_index(0u, 0u) + i] = 0u; g_dbg_wpos[dbg_ring_index(0u, 0u) + i] = i < NS ? i : 0xFFFFFFFFu; }
+#endif
         for (uint32_t i = tid; i < RCAP; i += THREADS) { ring0[i] = i < NS ? (ring_t)i : kRingSlotEmpty; ring1[i] = kRingSlotEmpty; if (BUNDLE) ring2[i] = kRingSlotEmpty; }
         if (tid == 0) {
             ctl->head[0] = 0; ctl->tail[0] = NS; ctl->avail[0] = NS;
@@ -319,9 +336,20 @@ render_pool(const __grid_constant__ KernelParams P) {
         pos = __shfl_sync(0xFFFFFFFFu, pos, 0);
         if (n == 0) break;
         ring_t *const ring = kind == 2u ? ring2 : (kind ? ring1 : ring0);
-        uint32_t id0 = lane < n ? pool_pop(ring, RCAP - 1u, pos + lane) : kRingEmpty;
-        uint32_t id1 = lane + 32u < n ? pool_pop(ring, RCAP - 1u, pos + 32u + lane) : kRingEmpty;
+        uint32_t id0 = lane < n ? pool_pop(ring, RCAP - 1u, pos + lane, kind) : kRingEmpty;
+        uint32_t id1 = lane + 32u < n ? pool_pop(ring, RCAP - 1u, pos + 32u + lane, kind) : kRingEmpty;
+        // Reconverge HERE.  A lane whose entry is still being written spins in pool_pop while the lanes that already hold
+        // their ids could run ahead -- there is no other full-mask operation before the end of the scan, so under independent
+        // thread scheduling the early lanes may finish a whole scan / refine / select before the late ones even read their
+        // entries.  Those entries then stay in the ring for a pass; the producers of the next lap queue up behind them, two
+        // producers end up waiting on one entry, both write when it is cleared, and a slot id is lost or taken twice.  Where
+        // the compiler places the convergence barrier after the spin loop is its choice: the release build happened to
+        // reconverge right after the loop, the -DSRT_SPIN_LIMIT build did not (found by scripts/soak.py on that build).
+        __syncwarp();
         __threadfence_block();
+        SRT_CHECK(16, (id0 == kRingEmpty || id0 < NS) && (id1 == kRingEmpty || id1 < NS));
+        if (id0 != kRingEmpty) SRT_OWN_SET(30, id0, 0u, 1u + (tid >> 5));
+        if (id1 != kRingEmpty) SRT_OWN_SET(30, id1, 0u, 1u + (tid >> 5));
 
         if (BUNDLE && kind == 2u) {
             // ---- up to 64 slots that delivered the last sample of a pixel chunk: fold the chunks, one per lane (A8, A9) ----
@@ -329,8 +357,14 @@ render_pool(const __grid_constant__ KernelParams P) {
 #pragma unroll 1
             for (int r = 0; r < 2; ++r) {
                 const uint32_t s = r ? id1 : id0;
-                if (s != kRingEmpty) fold_chunk(P, SRT_SU(S_PIX, s), SRT_SU(S_PXY, s), SRT_SU(S_K, s) >> P.bundle_log2);
+                if (s != kRingEmpty) {
+                    SRT_CHECKV(17, SRT_SU(S_PIX, s) < P.width * P.height, ((unsigned long long)SRT_SU(S_PIX, s) << 32) | (s << 16) | (SRT_SU(S_FLAGS, s) & 0xFFFFu));
+                    SRT_CHECK(18, SRT_SU(S_PXY, s) < P.band_items);
+                    SRT_CHECK(19, (SRT_SU(S_K, s) >> P.bundle_log2) < P.n_chunks);
+                    fold_chunk(P, SRT_SU(S_PIX, s), SRT_SU(S_PXY, s), SRT_SU(S_K, s) >> P.bundle_log2);
+                }
                 __syncwarp();
+                if (s != kRingEmpty) SRT_OWN_SET(31, s, 1u + (tid >> 5), 0u);
                 pool_push(ctl, ring0, RCAP - 1u, 0, s != kRingEmpty, s, lane);
             }
             hungry = false;
@@ -366,6 +400,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                         const uint32_t item = base + (r ? (uint32_t)(__popc(m0) + __popc(m1 & lt)) : (uint32_t)__popc(m0 & lt));
                         bool need = true;
                         if (item >= P.total_items) {                     // out of work: the slot retires
+                            SRT_OWN_SET(32, s, 1u + (tid >> 5), 0xFFFFu);
                             SRT_SU(S_PIX, s) = kInvalidPixel;
                             if (r) id1 = kRingEmpty; else id0 = kRingEmpty;
                             n_retired += 1u;
@@ -400,6 +435,7 @@ render_pool(const __grid_constant__ KernelParams P) {
                     // the same pixel, or the last chunk of the pixel at the same position one band earlier (bands are
                     // whole block rows: same column, inside the image as well)
                     bool row_free = true;
+                    SRT_CHECKV(23, pix < P.width * P.height, ((unsigned long long)pix << 32) | (s << 16) | (SRT_SU(S_FLAGS, s) & 0xFFFFu));
                     if (c != 0u) row_free = *(volatile uint32_t *)&P.done[pix] == (P.done_tag | c);
                     else if (pix >= P.band_pix) row_free = *(volatile uint32_t *)&P.done[pix - P.band_pix] == (P.done_tag | P.n_chunks);
                     if (row_free) {
@@ -581,11 +617,14 @@ render_pool(const __grid_constant__ KernelParams P) {
                     P.tap_prim[pix] = h.prim;
                 }
                 float4 sp = make_float4(0.f, 0.f, 0.f, 0.f);
+                SRT_CHECK(22, !h.hit || h.prim < P.n_pad);
                 if (h.hit) sp = STREAM ? __ldg(P.spheres + h.prim) : s_scan[h.prim];   // centre only; .w is not used by shading
                 ended = shade_scatter<true>(P, h, sp, o, d, atten, out, rng, bounce);
                 if (BUNDLE && ended) {
                     // stage the sample (S_K holds its ordinal); the slot that delivers the chunk's last one folds the chunk
                     const uint32_t row = SRT_SU(S_PXY, s), c = k >> P.bundle_log2;
+                    SRT_CHECK(20, row < P.band_items);
+                    SRT_CHECK(21, k < P.n_samples);
                     P.stage[((size_t)row << P.bundle_log2) + (k & ((1u << P.bundle_log2) - 1u))] = make_float4(out.x, out.y, out.z, 0.0f);
                     __threadfence();
                     folds = atomicAdd(&P.cnt[row], 1u) + 1u == min(1u << P.bundle_log2, P.n_samples - (c << P.bundle_log2));
@@ -605,6 +644,7 @@ render_pool(const __grid_constant__ KernelParams P) {
             {   // ONE copy of the push code for the three rings (they are contiguous in shared memory): the hot code sits right at
                 // the 32 KB of the L1.5 instruction cache; three inlined copies cost 1.6 % of the 4K / 256-spp launch
                 const int dest = folds ? 2 : (((valid && ended) || waits) ? 0 : ((valid && !ended) ? 1 : 3));
+                if (dest != 3) { SRT_OWN_SET(33, s, 1u + (tid >> 5), 0u); SRT_CHECKV(34, SRT_SU(S_PIX, s) < P.width * P.height, (s << 8) | (unsigned)dest); }
 #pragma unroll 1
                 for (int q = BUNDLE ? 2 : 1; q >= 0; --q) pool_push(ctl, ring0 + (uint32_t)q * RCAP, RCAP - 1u, q, dest == q, s, lane);
             }
@@ -825,6 +865,9 @@ typedef void (*render_kernel_t)(const KernelParams);
 // are made once, not per frame (the per-frame kick replaces WorkQueueStart, main.cpp:852 -- it has to be cheap).
 struct LaunchCfg { render_kernel_t kernel; int threads; size_t smem; int per_sm; };
 
+#ifdef SRT_SPIN_LIMIT
+static unsigned long long *g_spin_report_host = nullptr;   // host address of the word g_spin_report (device) points at
+#endif
 struct srt_backend {
     int device = -1;
     int sm_count = 0, clock_khz = 0;
@@ -1034,9 +1077,10 @@ static int create_resources(srt_backend *b) {
     SRT_CUDA(b, cudaEventCreate(&b->ev_stop));
     SRT_CUDA(b, cudaMalloc(&b->d_counters, 64));
     SRT_CUDA(b, cudaMemset(b->d_counters, 0, 64));
-    SRT_CUDA(b, cudaHostAlloc(&b->h_rays, 2 * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
+    SRT_CUDA(b, cudaHostAlloc(&b->h_rays, 4 * sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
     b->h_rays[0] = 0;                    // [0] rays of the last launch, [1] spin-limit report of the debug build
     b->h_rays[1] = 0;
+    b->h_rays[2] = 0;                    // [2] value attached to an index-check report
     {
         const int rc = resolve_static_scratch(b);            // set-up of srt_render_static: once per device, this device current
         if (rc != SRT_OK) return rc;
@@ -1045,6 +1089,7 @@ static int create_resources(srt_backend *b) {
     {
         unsigned long long *report = b->h_rays + 1;
         SRT_CUDA(b, cudaMemcpyToSymbol(g_spin_report, &report, sizeof(report)));
+        g_spin_report_host = report;         // the device symbol is per device, not per handle: the newest handle's word takes every report
     }
 #endif
     return SRT_OK;
@@ -1675,10 +1720,18 @@ int srt_wait(srt_backend *b, double *out_ms, uint64_t *out_rays) {
     if (e != cudaSuccess) {
         b->counters_dirty = true;
         std::string msg = std::string("srt_wait: ") + cudaGetErrorString(e);
-        const unsigned long long rep = *(volatile unsigned long long *)(b->h_rays + 1);
-        if ((rep >> 48) == 0xDEADull) {      // -DSRT_SPIN_LIMIT build: a wait loop gave up (site: 1 ring pop, 2 ring push, 3 acquire, 4 TMA barrier)
-            char buf[96];
-            snprintf(buf, sizeof(buf), "; spin limit exceeded at site %u (CTA %u, thread %u)", (unsigned)((rep >> 32) & 0xFFFFu), (unsigned)((rep >> 12) & 0xFFFFFu), (unsigned)(rep & 0xFFFu));
+        unsigned long long rep = *(volatile unsigned long long *)(b->h_rays + 1);
+#ifdef SRT_SPIN_LIMIT
+        unsigned long long rep_value = *(volatile unsigned long long *)(b->h_rays + 2);
+        if ((rep >> 48) != 0xDEADull && g_spin_report_host) { rep = *(volatile unsigned long long *)g_spin_report_host; rep_value = *(volatile unsigned long long *)(g_spin_report_host + 1); }
+#endif
+        if ((rep >> 48) == 0xDEADull) {      // -DSRT_SPIN_LIMIT build: a wait loop gave up (site: 1 ring pop, 2 ring push, 3 acquire, 4 TMA barrier) or an index check failed (site >= 16)
+            char buf[160];
+#ifdef SRT_SPIN_LIMIT
+            snprintf(buf, sizeof(buf), " [value 0x%llx]", rep_value);
+            msg += buf;
+#endif
+            snprintf(buf, sizeof(buf), "; spin limit exceeded or index check failed at site %u (CTA %u, thread %u)", (unsigned)((rep >> 32) & 0xFFFFu), (unsigned)((rep >> 12) & 0xFFFFFu), (unsigned)(rep & 0xFFFu));
             msg += buf;
         }
         return fail(b, SRT_ERR_CUDA, msg);

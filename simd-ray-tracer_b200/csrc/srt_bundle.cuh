@@ -117,6 +117,7 @@ __device__ __forceinline__ void bundle_scan(const float4 *__restrict__ tab, uint
             const int src = __ffs(nz) - 1;
             nz &= nz - 1u;
             const uint32_t m = __shfl_sync(0xFFFFFFFFu, word, src);
+            SRT_CHECK(26, qn < kPairsMaxWords);
             queue[qn] = make_uint2(m, (g0 + (uint32_t)src) << 2);
             qn += 1;
         }

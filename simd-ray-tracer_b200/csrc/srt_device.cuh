@@ -26,16 +26,21 @@ struct f3 { float x, y, z; };
 enum : uint32_t { kSpinPop = 1, kSpinPush = 2, kSpinAcquire = 3, kSpinMbar = 4 };
 #ifdef SRT_SPIN_LIMIT
 __device__ unsigned long long *g_spin_report;     // pinned + mapped host word of the handle that launched last
-__device__ __noinline__ void spin_fail(uint32_t site) {
+__device__ __noinline__ void spin_fail(uint32_t site, unsigned long long value = 0ull) {
     if (g_spin_report) {
+        *(volatile unsigned long long *)(g_spin_report + 1) = value;
         *(volatile unsigned long long *)g_spin_report = 0xDEAD000000000000ull | ((unsigned long long)site << 32) | (blockIdx.x << 12) | (threadIdx.x & 0xFFFu);
         __threadfence_system();
     }
     __trap();
 }
 #define SRT_SPIN(site, n) do { if (++(n) > (uint32_t)(SRT_SPIN_LIMIT)) spin_fail(site); } while (0)
+#define SRT_CHECK(site, cond) do { if (!(cond)) spin_fail(site); } while (0)      // index assertions of the debug build (sites >= 16)
+#define SRT_CHECKV(site, cond, value) do { if (!(cond)) spin_fail(site, (unsigned long long)(value)); } while (0)
 #else
 #define SRT_SPIN(site, n) do { (void)(n); } while (0)
+#define SRT_CHECK(site, cond) do { } while (0)
+#define SRT_CHECKV(site, cond, value) do { } while (0)
 #endif
 
 __device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }

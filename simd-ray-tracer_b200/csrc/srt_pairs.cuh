@@ -239,6 +239,7 @@ __device__ __forceinline__ void scan_slab_tile(const float4 *__restrict__ tile, 
         uint32_t m = 0;
 #pragma unroll
         for (int g = 0; g < 8; ++g) slab_group(m, 0x80000000u >> (4 * g), blk + 3 * g, r);
+        SRT_CHECK(24, qn < kPairsMaxWords);
         if (m) { queue[qn] = make_uint2(m, first + (c << 5)); qn += 1; }
     }
     if (count & 31u) {                       // tail: 2, 4 or 6 groups of 4
@@ -273,6 +274,7 @@ __device__ __forceinline__ void refine_queue(const Fetch &fetch_scan, CandQueue 
         const uint32_t j = (uint32_t)__clz((int)m);
         const uint32_t bit = 0x80000000u >> j;
         m &= ~bit;
+        SRT_CHECK(25, first + j < 65536u * 4u && qi <= qn && qn <= kPairsMaxWords);
         filter_sphere(keep, bit, fetch_scan(first + j), r.p2ox, r.p2oy, r.p2oz, r.dx, r.dy, r.dz, r.od, r.ooa, r.oob);
     }
     qn = qo;

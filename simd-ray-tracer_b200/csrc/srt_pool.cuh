@@ -18,6 +18,11 @@
 //         ring[pos+i] != EMPTY; read id; write EMPTY
 // avail counts published ids, so [head, head+n) has always been reserved by producers that
 // are a few instructions away from writing it: both waits are short and cannot deadlock.
+// "Short" is load-bearing: an entry that stays unread for a whole lap of its ring lets the producers of two laps wait on
+// it together, and both write when it is cleared.  So every lane of a warp must be past its spin before the warp moves on:
+// pool_push ends in __syncwarp(), and the caller of pool_pop reconverges right after the pops (render_pool) -- without
+// that, the lanes that already hold their ids may run a whole scan while the others have not even read their entries.
+// The -DSRT_SPIN_LIMIT build audits all of this per entry (g_dbg_* below).
 // With kPoolSlots = 64 * (warps + 2) one of the rings always holds a full batch while the
 // other warps are busy.
 #pragma once
@@ -42,6 +47,20 @@ struct PoolCtl {
     unsigned int scanning[4];                  // warps of each SM sub-partition (warp id % 4) that are inside a per-ray slab scan
 };
 
+#ifdef SRT_SPIN_LIMIT
+// Debug build (-DSRT_SPIN_LIMIT): shadow state that audits the ring protocol, indexed by (CTA, ring, physical entry).
+//   g_dbg_wpos   the absolute position the entry was last written for: a pop must find its own position (site 40), a push
+//                must not find its own (site 42: one position written twice)
+//   g_dbg_busy   1 + lap of the consumer that is inside pool_pop on the entry: two at once (site 35) means the consumers
+//                of two laps met on one entry, i.e. an entry stayed unread for a whole lap
+// plus: a pop re-reads the entry after clearing it (site 41), and neither wait may last longer than kDbgWaitCycles
+// (sites 36 pop, 37 push) -- the protocol's claim is that both waits are short.  Sites 16-34 are in srt_backend.cu.
+constexpr unsigned int kDbgRingEntries = 2048u, kDbgCtas = 1024u;     // grids are one resident wave: <= 148 SMs x 2 CTAs here (site 15 checks)
+constexpr long long kDbgWaitCycles = 400000ll;            // 0.2 ms; a warp pass is 20-50 us
+__device__ unsigned int g_dbg_wpos[kDbgCtas * 3 * kDbgRingEntries];
+__device__ unsigned int g_dbg_busy[kDbgCtas * 3 * kDbgRingEntries];
+__device__ __forceinline__ unsigned int dbg_ring_index(uint32_t q, uint32_t entry) { return ((blockIdx.x % kDbgCtas) * 3u + q) * kDbgRingEntries + entry; }
+#endif
 // Inline on purpose: an out-of-line copy (one instead of seven in pool_acquire) measured 6 % slower.
 __device__ __forceinline__ bool pool_try_take(PoolCtl *ctl, int q, uint32_t want_min, uint32_t &n, uint32_t &pos) {
     unsigned int old = *(volatile unsigned int *)&ctl->avail[q];
@@ -123,12 +142,38 @@ __device__ __forceinline__ void pool_acquire(PoolCtl *ctl, uint32_t n_slots, boo
     }
 }
 
-__device__ __forceinline__ uint32_t pool_pop(ring_t *ring, uint32_t cap_mask, uint32_t pos) {
+__device__ __forceinline__ uint32_t pool_pop(ring_t *ring, uint32_t cap_mask, uint32_t pos, [[maybe_unused]] uint32_t q) {
     volatile ring_t *e = ring + (pos & cap_mask);
     ring_t id;
     [[maybe_unused]] uint32_t spins = 0;
-    while ((id = *e) == kRingSlotEmpty) { SRT_SPIN(kSpinPop, spins); }
+#ifdef SRT_SPIN_LIMIT
+    unsigned int *busy = &g_dbg_busy[dbg_ring_index(q, pos & cap_mask)];
+    const unsigned int was = atomicExch(busy, 1u + pos / (cap_mask + 1u));
+    SRT_CHECKV(35, was == 0u, ((unsigned long long)was << 32) | (q << 28) | pos);
+    const long long t0 = clock64();
+#endif
+    while ((id = *e) == kRingSlotEmpty) {
+        SRT_SPIN(kSpinPop, spins);
+#ifdef SRT_SPIN_LIMIT
+        SRT_CHECKV(36, clock64() - t0 < kDbgWaitCycles, ((unsigned long long)q << 60) | pos);
+#endif
+    }
+#ifdef SRT_SPIN_LIMIT
+    {
+        const unsigned int w = atomicAdd(&g_dbg_wpos[dbg_ring_index(q, pos & cap_mask)], 0u);
+        SRT_CHECKV(40, w == pos, ((unsigned long long)q << 62) | ((unsigned long long)w << 30) | ((unsigned long long)(pos & 0x3FFFFFu) << 8) | (id & 0xFFu));
+    }
+#endif
     *e = kRingSlotEmpty;
+#ifdef SRT_SPIN_LIMIT
+    __threadfence_block();
+    {
+        const ring_t again = *e;
+        const unsigned int w2 = atomicAdd(&g_dbg_wpos[dbg_ring_index(q, pos & cap_mask)], 0u);
+        SRT_CHECKV(41, again == kRingSlotEmpty || w2 != pos, ((unsigned long long)q << 62) | ((unsigned long long)again << 40) | ((unsigned long long)id << 24) | (pos & 0xFFFFFFu));
+    }
+    atomicExch(busy, 0u);
+#endif
     return id;
 }
 
@@ -141,13 +186,29 @@ __device__ __forceinline__ void pool_push(PoolCtl *ctl, ring_t *ring, uint32_t c
     if (lane == leader) pos = atomicAdd(&ctl->tail[q], __popc(m));
     pos = __shfl_sync(0xFFFFFFFFu, pos, leader);
     if (doit) {
-        volatile ring_t *e = ring + ((pos + __popc(m & ((1u << lane) - 1u))) & cap_mask);
+        const uint32_t mine = pos + __popc(m & ((1u << lane) - 1u));
+        volatile ring_t *e = ring + (mine & cap_mask);
         [[maybe_unused]] uint32_t spins = 0;
-        while (*e != kRingSlotEmpty) { SRT_SPIN(kSpinPush, spins); }
+#ifdef SRT_SPIN_LIMIT
+        const long long t0 = clock64();
+#endif
+        while (*e != kRingSlotEmpty) {
+            SRT_SPIN(kSpinPush, spins);
+#ifdef SRT_SPIN_LIMIT
+            SRT_CHECKV(37, clock64() - t0 < kDbgWaitCycles, ((unsigned long long)q << 60) | ((unsigned long long)*e << 32) | mine);
+#endif
+        }
+#ifdef SRT_SPIN_LIMIT
+        {
+            const unsigned int oldw = atomicExch(&g_dbg_wpos[dbg_ring_index((uint32_t)q, mine & cap_mask)], mine);
+            SRT_CHECKV(42, oldw != mine, ((unsigned long long)q << 62) | ((unsigned long long)id << 32) | mine);
+            __threadfence();
+        }
+#endif
         *e = (ring_t)id;
     }
     __threadfence_block();
-    __syncwarp();
+    __syncwarp();                 // every lane has written (and is past its wait) before the ids are announced
     if (lane == leader) atomicAdd(&ctl->avail[q], __popc(m));
 }
 

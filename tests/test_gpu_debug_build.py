@@ -41,3 +41,29 @@ def test_debug_library_renders_the_same_bits(srt):
         assert r.returncode == 0, r.stderr
         res.append(r.stdout.strip().splitlines()[-1])
     assert res[0] == res[1]
+
+
+def test_audited_ring_protocol_under_load(srt):
+    """scripts/soak.py on the debug library: jobs that fill the machine (1,024 and 482 spheres, bundle mode, several frames),
+    every ring push / pop audited (slot ownership, one consumer per entry, the position an entry was written for, no wait
+    longer than 0.2 ms), every job twice, then the hashes against the release library's.  Before the __syncwarp() after the
+    ring pops this failed within the first 20 jobs."""
+    dbg = os.path.join(srt.PKG_DIR, "libsrt_cuda_dbg.so")
+    out = {}
+    for tag, lib in (("release", None), ("debug", dbg)):
+        env = dict(os.environ)
+        env.pop("SRT_CUDA_LIB", None)
+        if lib:
+            env["SRT_CUDA_LIB"] = lib
+        hashes = []
+        for n, (fixed, cases) in enumerate((("1024,943,409,64,3", 12), ("482,687,446,33,2", 30), ("", 60))):
+            path = os.path.join(ROOT, "gpurun_out", f"soak_test_{tag}_{n}.json")
+            cmd = [sys.executable, os.path.join(ROOT, "scripts", "soak.py"), "--cases", str(cases), "--modes", "8:1", "--out", path]
+            if fixed:
+                cmd += ["--fixed", fixed]
+            r = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=900)
+            assert r.returncode == 0, (tag, fixed, r.stdout[-600:], r.stderr[-600:])
+            with open(path) as f:
+                hashes.append(__import__("json").load(f)["cases"])
+        out[tag] = hashes
+    assert out["release"] == out["debug"]
