@@ -69,16 +69,28 @@ def main():
         h = int(rng.integers(1, 300 if big else 800))
         spp = int(rng.choice([1, 1, 2, 7, 8, 9, 16, 33] if big else [1, 1, 2, 7, 8, 9, 16, 33, 64]))
         frames = int(rng.integers(1, 4))
+        # the other launch parameters of the C ABI: sample stride / offset (sample partition), sum mode, image partition
+        # (this handle renders part `part` of `n_parts`), the no-allocation entry point, the primary-ray taps
+        stride = int(rng.choice([1, 1, 1, 2, 3]))
+        offset = int(rng.integers(stride))
+        mode = srt.ACCUM_SUM if (rng.random() < 0.2 or stride > 1) else srt.ACCUM_MEAN      # the exact running mean needs stride 1
+        n_parts = int(rng.choice([1, 1, 2, 3, 4]))
+        part = int(rng.integers(n_parts))
+        static = bool(rng.random() < 0.2)
+        taps = bool(rng.random() < 0.15)
         if args.fixed:
             n, w, h, spp, frames = (int(x) for x in args.fixed.split(","))
             n = min(n, len(sp))
+            stride, offset, mode, n_parts, part, static, taps = 1, 0, srt.ACCUM_MEAN, 1, 0, False, False
         cam = srt.host_camera(3, w, h, hdr3)
         if case < args.first:
             continue
         b.set_scene(sp[:n].copy(), sky, W, bool(fma))
         b.resize(w, h)
+        b.set_partition(part, n_parts)
+        static = static and w * h <= srt.STATIC_MAX_PIXELS
         got = []
-        key = f"{case}:n{n}_W{W}f{fma}_{w}x{h}_{spp}spp_x{frames}"
+        key = f"{case}:n{n}_W{W}f{fma}_{w}x{h}_{spp}spp_x{frames}_s{stride}+{offset}_m{mode}_p{part}/{n_parts}{'_static' if static else ''}{'_taps' if taps else ''}"
         if args.verbose:
             print(key, flush=True)
         try:
@@ -86,9 +98,14 @@ def main():
                 b.reset()
                 rays = 0
                 for f in range(frames):
-                    b.render(cam, f * spp, spp)
+                    first = offset + f * spp * stride
+                    if static:
+                        b.render_static(cam, first, spp, stride=stride, mode=mode)
+                    else:
+                        b.render(cam, first, spp, stride=stride, mode=mode, record_primary=taps and f == 0)
                     rays += b.wait()[1]
-                got.append((sha(b.read_accum()), sha(b.read_rgba8()), int(rays)))
+                extra = sha(np.concatenate([x.view(np.uint32).ravel() for x in b.read_primary()])) if taps and not static else ""
+                got.append((sha(b.read_accum()), sha(b.read_rgba8()), int(rays), extra))
         except Exception as e:
             print("FAILED", key, b.last_kernel(), e, flush=True)
             sys.exit(3)
@@ -97,12 +114,13 @@ def main():
             sys.exit(2)
         out[key] = list(got[0]) + [b.last_kernel()]
         rays_total += got[0][2] * 2
+        b.set_partition(0, 1)
     for b in handles:
         b.close()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     with open(args.out, "w") as f:
         json.dump({"lib": os.environ.get("SRT_CUDA_LIB", "release"), "seconds": round(time.time() - t0, 1), "rays": rays_total, "cases": out}, f, indent=0)
-    kernels = sorted({v[3] for v in out.values()})
+    kernels = sorted({v[-1] for v in out.values()})
     print(f"{len(out)} cases, {rays_total / 1e9:.2f} G rays, {time.time() - t0:.1f} s, {len(kernels)} kernels", flush=True)
 
 
