@@ -155,6 +155,8 @@ int srt_resolve_sum(srt_backend *b, uint32_t total_samples);
 int srt_read_rgba8(srt_backend *b, void *dst /* W*H*4 bytes */);
 int srt_read_accum(srt_backend *b, float *dst /* W*H*4 floats */);
 int srt_read_primary(srt_backend *b, uint32_t *prim /* 0xFFFFFFFF = miss */, float *t /* 1e30 = miss */);
+/* Under an image partition (srt_set_partition, n_parts > 1) the pixels of the other parts read back with all bits set
+ * in both buffers (prim 0xFFFFFFFF, t = the NaN 0xFFFFFFFF); a handle that owns no row at all still answers. */
 /* Upload a HOST accumulator (W*H*4 floats, as srt_read_accum returned it) into PreviousImage:
  * resume an interrupted accumulation -- the next srt_render continues with
  * first_sample = the number of samples the buffer holds (checkpoint/resume; the reference keeps

@@ -1499,6 +1499,20 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     rc = drain(b);
     if (rc) return rc;
     b->gathered_rgba = b->gathered_accum = false;
+    if (args->record_primary) {
+        const size_t n = (size_t)b->width * b->height;
+        if (!b->d_tap_prim) {
+            SRT_CUDA(b, cudaMalloc(&b->d_tap_prim, n * sizeof(uint32_t)));
+            SRT_CUDA(b, cudaMalloc(&b->d_tap_t, n * sizeof(float)));
+        }
+        if (b->n_parts > 1u) {            // image partition: the rows of the other devices read as "not rendered here" (all bits set)
+            SRT_CUDA(b, cudaMemsetAsync(b->d_tap_prim, 0xFF, n * sizeof(uint32_t), b->stream));
+            SRT_CUDA(b, cudaMemsetAsync(b->d_tap_t, 0xFF, n * sizeof(float), b->stream));
+        }
+        P.tap_prim = b->d_tap_prim;
+        P.tap_t = b->d_tap_t;
+        b->tap_valid = true;
+    }
     if (P.total_items == 0u) {            // more devices than block rows: this handle owns no pixel
         *b->h_rays = 0;
         b->events_recorded = false;
@@ -1521,16 +1535,6 @@ int srt_render(srt_backend *b, const srt_camera *cam, const srt_render_args *arg
     if (!pool && (size_t)b->n_pad * sizeof(float4) > b->max_smem_optin)
         return fail(b, SRT_ERR_TOO_LARGE, "srt_render: scene too large for the one-path kernel");
     if (packed) P.spheres = b->d_spheres2;
-    if (args->record_primary) {
-        const size_t n = (size_t)b->width * b->height;
-        if (!b->d_tap_prim) {
-            SRT_CUDA(b, cudaMalloc(&b->d_tap_prim, n * sizeof(uint32_t)));
-            SRT_CUDA(b, cudaMalloc(&b->d_tap_t, n * sizeof(float)));
-        }
-        P.tap_prim = b->d_tap_prim;
-        P.tap_t = b->d_tap_t;
-        b->tap_valid = true;
-    }
 
     bool use_bundle = false;
     if (!K.pool_debug) P.debug = nullptr;

@@ -175,3 +175,33 @@ def test_headless_driver_on_two_gpus_is_byte_identical(srt, tmp_path):
         assert stats["gpus"] == g
         outs.append((ppm.read_bytes(), acc.read_bytes(), stats["rays"]))
     assert outs[0] == outs[1]
+
+
+def test_primary_taps_under_an_image_partition(srt, oracle):
+    """record_primary with srt_set_partition on one device: own rows equal the unpartitioned taps, foreign rows read as all
+    bits set, and a part that owns no row at all (image lower than n_parts block rows) still answers (found by scripts/soak.py)."""
+    sp, sky, hdr = oracle.scene(2)
+    b = srt.Backend(0)
+    try:
+        b.set_scene(sp, sky, 8, True)
+        for (w, h, n_parts) in ((96, 40, 3), (50, 3, 2)):
+            cam = oracle.camera(hdr, w, h)
+            b.resize(w, h)
+            b.set_partition(0, 1)
+            b.reset()
+            b.render(cam, 0, 2, record_primary=True)
+            b.wait()
+            prim_all, t_all = b.read_primary()
+            rows = np.arange(h)
+            for part in range(n_parts):
+                b.set_partition(part, n_parts)
+                b.reset()
+                b.render(cam, 0, 2, record_primary=True)
+                b.wait()
+                prim, t = b.read_primary()
+                own = ((rows // 4) % n_parts) == part
+                assert np.array_equal(prim[own], prim_all[own]) and np.array_equal(t[own].view(np.uint32), t_all[own].view(np.uint32))
+                assert (prim[~own] == 0xFFFFFFFF).all() and (t[~own].view(np.uint32) == 0xFFFFFFFF).all()
+    finally:
+        b.set_partition(0, 1)
+        b.close()
