@@ -143,7 +143,7 @@ def build(verbose=True):
             print(f"[build_ref] {REF} absent: keeping prebuilt oracle/_ref as is")
         return False
     os.makedirs(OUT, exist_ok=True)
-    tmp = tempfile.mkdtemp(prefix="srt_ref_")
+    tmp = tempfile.mkdtemp(prefix=".patched_", dir=OUT)   # inside oracle/_ref (git-ignored), removed below: nothing is written outside the repository
     try:
         for name, text in patched_sources().items():
             with open(os.path.join(tmp, name), "w", encoding="utf-8") as f:

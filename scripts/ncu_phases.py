@@ -1,5 +1,5 @@
 """ncu source page joined with nvdisasm line info: share of instructions / issue cycles / stall samples per source line.
-usage: cuobjdump -xelf all libsrt_cuda.so && nvdisasm --print-line-info srt_backend.sm_100a.cubin > /tmp/all_dis.txt
+usage: cuobjdump -xelf all libsrt_cuda.so && nvdisasm --print-line-info srt_backend.sm_100a.cubin > gpurun_out/all_dis.txt
        python scripts/ncu_phases.py report.ncu-rep <mangled kernel name>"""
 import csv, io, re, subprocess, sys, collections
 rep = sys.argv[1]; kern = sys.argv[2]
@@ -7,7 +7,7 @@ out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_ou
 lines = out.splitlines()
 start = next(i for i, l in enumerate(lines) if l.startswith('"Address"'))
 rows = list(csv.DictReader(io.StringIO("\n".join(lines[start:]))))
-dl = open('/tmp/all_dis.txt').read().splitlines()
+dl = open('gpurun_out/all_dis.txt').read().splitlines()
 s = next(i for i,l in enumerate(dl) if l.startswith('.text.'+kern))
 cur=None; li=[]
 for l in dl[s+1:]:
